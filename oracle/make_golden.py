@@ -1,0 +1,90 @@
+#!/usr/bin/env python
+"""Generate the committed golden fixtures under tests/golden/ by RUNNING THE
+REFERENCE ITSELF (oracle/_ref/lda_ref = the unmodified oni-lda-c sources built
+by oracle/ref_build/Makefile) on small synthetic corpora.
+
+TEST INFRASTRUCTURE ONLY.  Run from the repo root, in the build container
+(where /root/reference exists):
+
+    make -C oracle && python oracle/make_golden.py
+
+The reference has no tests or golden vectors of its own,
+so these outputs are the parity pins: 000.beta pins the RNG, the random
+initialisation and lda_mle; likelihood.dat line i pins the E-step at EM
+iteration i (line 1 needs only the initialisation and one E-step) and, from
+line 2 on, the reduction, M-step and alpha Newton; final.* pin the whole run.
+"""
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oni_ml_b200.corpus import Corpus, synth_corpus, write_model_dat  # noqa: E402
+
+REF = os.path.join(ROOT, "oracle", "_ref", "lda_ref")
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+SETTINGS_SHIPPED = ("var max iter 20\nvar convergence 1e-6\nem max iter 20\n"
+                    "em convergence 1e-6\nalpha estimate\n")  # oni-lda-c/settings.txt
+SETTINGS_FIXED = ("var max iter 5\nvar convergence 1e-4\nem max iter 6\n"
+                  "em convergence 1e-5\nalpha fixed\n")
+SETTINGS_UNBOUNDED = ("var max iter -1\nvar convergence 1e-6\nem max iter 4\n"
+                      "em convergence 1e-4\nalpha estimate\n")  # cf. inf-settings.txt
+
+
+def run_ref(model, settings_text, alpha, k, seed, nproc, keep, outdir):
+    with tempfile.TemporaryDirectory() as tmp:
+        st = os.path.join(tmp, "settings.txt")
+        with open(st, "w") as f:
+            f.write(settings_text)
+        out = os.path.join(tmp, "out")
+        env = dict(os.environ, ONI_LDA_SEED=str(seed), ONI_MPI_NP=str(nproc))
+        subprocess.run([REF, "est", alpha, str(k), st, str(nproc), model, "random", out],
+                       check=True, env=env, stdout=subprocess.DEVNULL)
+        os.makedirs(outdir, exist_ok=True)
+        with open(os.path.join(outdir, "settings.txt"), "w") as f:
+            f.write(settings_text)
+        with open(os.path.join(outdir, "args.txt"), "w") as f:
+            f.write("alpha %s\nk %d\nseed %d\nnproc %d\n" % (alpha, k, seed, nproc))
+        for name in keep:
+            shutil.copy(os.path.join(out, name), os.path.join(outdir, name))
+
+
+def main():
+    os.makedirs(GOLD, exist_ok=True)
+    c = synth_corpus(400, 300, k_true=8, mu=2.0, seed=20160122)
+    # edge cases the grammar allows: an empty document, a one-word document and
+    # a document made of one repeated word id (kept as separate pairs)
+    ptr = c.doc_ptr.tolist()
+    word = c.word.tolist()
+    count = c.count.tolist()
+    for w_list, c_list in (([], []), ([7], [3]), ([11, 11, 11], [1, 2, 5])):
+        word += w_list
+        count += c_list
+        ptr.append(len(word))
+    c = Corpus(np.asarray(ptr, np.int64), np.asarray(word, np.int32),
+               np.asarray(count, np.int32), 300)
+    model = os.path.join(GOLD, "c0_model.dat")
+    write_model_dat(model, c)
+
+    everything = ["000.beta", "000.other", "likelihood.dat", "final.beta", "final.gamma",
+                  "final.other"]
+    run_ref(model, SETTINGS_SHIPPED, "2.5", 20, 4357, 1, everything,
+            os.path.join(GOLD, "c0_k20"))
+    run_ref(model, SETTINGS_SHIPPED, "2.5", 20, 4357, 3,
+            ["likelihood.dat", "final.other"], os.path.join(GOLD, "c0_k20_np3"))
+    run_ref(model, SETTINGS_FIXED, "0.1", 5, 99, 1,
+            ["000.other", "likelihood.dat", "final.gamma", "final.other"],
+            os.path.join(GOLD, "c0_k5_fixed"))
+    run_ref(model, SETTINGS_UNBOUNDED, "1.0", 37, 12345, 1,
+            ["likelihood.dat", "final.other"], os.path.join(GOLD, "c0_k37_unbounded"))
+    print("golden fixtures written to", GOLD)
+
+
+if __name__ == "__main__":
+    main()
