@@ -1,0 +1,276 @@
+/*
+ * oni_lda.h -- C ABI of the B200-native variational-EM LDA engine and event
+ * scorer that replaces the oni-lda-c step of rabarona/oni-ml.
+ *
+ * The reference has no in-process interface for this path: its "plugin API" is
+ * a process command line plus files (ml_ops.sh:79-80 launches
+ * `mpiexec ... ./lda est 2.5 20 settings.txt 20 model.dat random <dir>`), and
+ * the scoring loop is a spark-shell script (ml_ops.sh:108).  This header is the
+ * FFI a maintainer of that pipeline would bind instead (see INTEGRATION.md for
+ * the ml_ops.sh edit, a JNI/JNA stub for the Scala stage and a ctypes stub).
+ * Each entry point names the reference code it stands in for; paths are
+ * relative to the reference repository root.
+ *
+ * Conventions
+ *   - plain C: pointers, sizes, PODs; no C++ or framework types cross the ABI;
+ *   - every function returns 0 on success and a non-zero oni_status otherwise;
+ *     oni_last_error() then returns a message (thread-local).  The reference
+ *     never reports failure (main always returns 0, lda-estimate.c:467), so any
+ *     caller that ignored the status keeps working;
+ *   - "host" pointers are ordinary process memory, "device" pointers are CUDA
+ *     global memory on the context's device;
+ *   - matrices are row-major doubles.  Topic-major [K][V] is the layout of the
+ *     reference's log_prob_w / class_word (lda.h:40-57) and of final.beta;
+ *   - there is no CPU fallback: without a CUDA device the compute entry points
+ *     fail with ONI_ERR_CUDA.
+ */
+#ifndef ONI_LDA_H
+#define ONI_LDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    ONI_OK = 0,
+    ONI_ERR_ARG = 1,    /* bad argument / size                               */
+    ONI_ERR_IO = 2,     /* file missing, unreadable, malformed, unwritable   */
+    ONI_ERR_CUDA = 3,   /* CUDA runtime error, or no device                  */
+    ONI_ERR_NCCL = 4,   /* NCCL not loadable or a collective failed          */
+    ONI_ERR_NAN = 5,    /* a document bound became NaN (the reference aborts
+                           on assert(!isnan), lda-inference.c:78)            */
+    ONI_ERR_NOMEM = 6
+} oni_status;
+
+/* Message for the last failure on the calling thread ("" if none). */
+const char *oni_last_error(void);
+
+/* Version string of the library ("oni-lda-b200 x.y"). */
+const char *oni_version(void);
+
+/* ------------------------------------------------------------------------ */
+/* settings.txt  (read_settings, oni-lda-c/lda-estimate.c:331-350)           */
+/* The two thresholds are floats in the reference (lda-inference.h:10,       */
+/* lda-estimate.h:21) and are compared after promotion to double.            */
+typedef struct {
+    int32_t var_max_iter;   /* "var max iter %d"      (-1 = no cap)           */
+    float var_converged;    /* "var convergence %f"                           */
+    int32_t em_max_iter;    /* "em max iter %d"                               */
+    float em_converged;     /* "em convergence %f"                            */
+    int32_t estimate_alpha; /* "alpha %s": 0 for the literal "fixed", else 1  */
+} oni_lda_settings;
+
+int oni_lda_read_settings(const char *path, oni_lda_settings *out);
+
+/* ------------------------------------------------------------------------ */
+/* Corpus in host memory, CSR.  Replaces document/corpus (lda.h:23-37) and    */
+/* read_data (lda-data.c:22-59).  Duplicate word ids inside a document are    */
+/* separate pairs.  num_terms = largest word id + 1 (lda-data.c:49).          */
+typedef struct {
+    int32_t num_docs;
+    int32_t num_terms;
+    int64_t nnz;
+    const int64_t *doc_ptr; /* [num_docs+1]                                  */
+    const int32_t *word;    /* [nnz]                                         */
+    const int32_t *count;   /* [nnz]                                         */
+} oni_lda_corpus;
+
+/* Parse model.dat ("N w:c w:c ..." per line).  The arrays are malloc'ed by the
+ * library; release them with oni_lda_free_corpus. */
+int oni_lda_read_corpus(const char *model_dat_path, oni_lda_corpus *out);
+void oni_lda_free_corpus(oni_lda_corpus *c);
+
+/* ------------------------------------------------------------------------ */
+/* Whole-run entry points                                                    */
+
+/* The reference's process entry (main, lda-estimate.c:403-468) with the same
+ * argv:   lda est <alpha> <k> <settings> <ngpus> <model.dat> <random|seeded|root> <outdir>
+ *         lda inf <settings> <model_root> <model.dat> <out_name>
+ * argv[5] ("#processes", the MPI stride of lda-estimate.c:201,428) is read as
+ * the number of GPUs to shard documents over.  The RNG seed is the wall clock
+ * as in the reference (lda-estimate.c:414-416) unless the environment variable
+ * ONI_LDA_SEED is set.  Writes <outdir>/000.beta, 000.other, likelihood.dat,
+ * final.beta, final.other, final.gamma (formats of lda-model.c:193-217,
+ * lda-estimate.c:88-104,266).  Returns 0 or an oni_status. */
+int oni_lda_main(int argc, char **argv);
+
+/* Result of an in-memory estimation; all arrays are caller-allocated host
+ * memory (any pointer may be NULL to skip that output). */
+typedef struct {
+    double *logbeta_init;  /* [K][V]  model before EM (000.beta)             */
+    double *logbeta;       /* [K][V]  final.beta                             */
+    double *gamma;         /* [D][K]  final.gamma                            */
+    double *likelihood;    /* [likelihood_cap] bound after each EM iteration */
+    double *converged;     /* [likelihood_cap] relative change (first = inf) */
+    int32_t likelihood_cap;
+    int32_t em_iters;      /* out: EM iterations run                         */
+    double alpha;          /* out: final alpha (final.other)                 */
+    double seconds_em;     /* out: wall time of the EM loop                  */
+} oni_lda_result;
+
+/* run_em (lda-estimate.c:112-321) for start = "random", over host buffers:
+ * uploads the corpus, initialises the model with the reference's MT19937
+ * stream (cokus.c, lda-model.c:104-117), runs EM on `ngpus` GPUs of this
+ * process (documents sharded, one NCCL all-reduce of the sufficient statistics
+ * per iteration when ngpus > 1), downloads the results.
+ * initial_alpha is used as given (the CLI rounds it through float as
+ * lda-estimate.c:425 does). */
+int oni_lda_estimate(const oni_lda_corpus *corpus, int32_t num_topics, double initial_alpha,
+                     const oni_lda_settings *settings, uint32_t seed, int32_t ngpus,
+                     oni_lda_result *result);
+
+/* ------------------------------------------------------------------------ */
+/* Step-wise engine (one context = one GPU = one shard of the documents).     */
+/* This is what a host that owns the process layout (one process per GPU,     */
+/* e.g. under torchrun) drives; oni_lda_estimate is built on it.              */
+typedef struct oni_lda_ctx oni_lda_ctx;
+
+/* new_lda_model + new_lda_suffstats (lda-model.c:151-168,61-80) on `device`. */
+int oni_lda_create(int32_t device, int32_t num_topics, int32_t num_terms,
+                   const oni_lda_settings *settings, oni_lda_ctx **out);
+void oni_lda_destroy(oni_lda_ctx *ctx);
+
+/* Shard of documents for this context, from host CSR arrays (copied) ...     */
+int oni_lda_set_corpus(oni_lda_ctx *ctx, int32_t num_docs, int64_t nnz, const int64_t *doc_ptr,
+                       const int32_t *word, const int32_t *count);
+/* ... or from arrays already resident on the context's device (copied d2d). */
+int oni_lda_set_corpus_device(oni_lda_ctx *ctx, int32_t num_docs, int64_t nnz,
+                              const int64_t *d_doc_ptr, const int32_t *d_word,
+                              const int32_t *d_count);
+
+/* random_initialize_ss + lda_mle(model, ss, 0) + alpha = initial
+ * (lda-estimate.c:155-161): bit-identical to the reference for the same seed. */
+int oni_lda_init_random(oni_lda_ctx *ctx, uint32_t seed, double initial_alpha);
+/* Start from a given model: logbeta host [K][V] (load_lda_model semantics are
+ * the caller's business), alpha. */
+int oni_lda_set_model(oni_lda_ctx *ctx, const double *logbeta, double alpha);
+
+/* E-step over the shard (doc_e_step for every document, lda-estimate.c:201-208,
+ * 28-60; lda_inference + compute_likelihood, lda-inference.c:27-127) followed by
+ * the deterministic reduction into the packed sufficient-statistics buffer.
+ * Asynchronous on the context's stream. */
+int oni_lda_e_step(oni_lda_ctx *ctx);
+
+/* The packed sufficient statistics of the last E-step, on the device:
+ *   [num_terms*KP] class_word, word-major, KP = num_topics rounded up to 4
+ *   [KP]           class_total
+ *   [1] alpha_suffstats  [1] likelihood  [1] num_docs  [1] word visits
+ * This is the operand of the one all-reduce per EM iteration that replaces the
+ * 2K+3 MPI_Allreduce calls of lda-estimate.c:211-252.  *count = doubles. */
+int oni_lda_suffstats(oni_lda_ctx *ctx, double **d_buffer, size_t *count);
+
+/* NCCL plumbing for one-process-per-GPU hosts: rank 0 makes an id, the host
+ * broadcasts the bytes by its own means, every rank calls comm_init. */
+#define ONI_NCCL_ID_BYTES 128
+int oni_lda_comm_unique_id(unsigned char id[ONI_NCCL_ID_BYTES]);
+int oni_lda_comm_init(oni_lda_ctx *ctx, const unsigned char id[ONI_NCCL_ID_BYTES],
+                      int32_t rank, int32_t nranks);
+/* Sum the packed buffer over all ranks (no-op without a communicator). */
+int oni_lda_allreduce(oni_lda_ctx *ctx);
+
+/* M-step: lda_mle (lda-model.c:27-54) incl. opt_alpha (lda-alpha.c:42-68) when
+ * settings.estimate_alpha == 1, on the device; then the convergence bookkeeping
+ * of lda-estimate.c:260-262 (relative change; var_max_iter doubles when the
+ * bound decreased).  Synchronises; returns the bound and its relative change. */
+int oni_lda_m_step(oni_lda_ctx *ctx, double *likelihood, double *converged);
+
+/* e_step + allreduce + m_step. */
+int oni_lda_em_iteration(oni_lda_ctx *ctx, double *likelihood, double *converged);
+
+/* 1 while the loop condition of lda-estimate.c:186 holds. */
+int oni_lda_em_should_continue(const oni_lda_ctx *ctx);
+
+/* Readback (host buffers).  gamma is [shard docs][K] in shard order. */
+int oni_lda_get_logbeta(oni_lda_ctx *ctx, double *logbeta /* [K][V] */);
+int oni_lda_get_gamma(oni_lda_ctx *ctx, double *gamma /* [D][K] */);
+int oni_lda_get_alpha(oni_lda_ctx *ctx, double *alpha);
+int oni_lda_get_doc_likelihood(oni_lda_ctx *ctx, double *lik /* [D] */);
+/* Per-document variational passes of the last E-step (diagnostics). */
+int oni_lda_get_doc_iters(oni_lda_ctx *ctx, int32_t *iters /* [D] */);
+
+/* Timing / accounting of the last E-step, for the bench. */
+typedef struct {
+    double ms_estep_kernel;  /* CUDA-event time of the per-document kernel    */
+    double ms_suffstats;     /* deterministic reduction kernels               */
+    double ms_mstep;         /* M-step + alpha kernels                        */
+    int64_t word_visits;     /* sum over docs of pairs x passes               */
+    int64_t kernel_launches; /* kernels launched by the library so far        */
+} oni_lda_stats;
+int oni_lda_get_stats(oni_lda_ctx *ctx, oni_lda_stats *out);
+/* The CUDA stream (cudaStream_t) every kernel of this context is launched on,
+ * so a host can bracket steps with its own events. */
+int oni_lda_stream(oni_lda_ctx *ctx, void **cuda_stream);
+
+/* ------------------------------------------------------------------------ */
+/* File writers (save_lda_model lda-model.c:193-217, save_gamma              */
+/* lda-estimate.c:88-104).  logbeta [K][V], gamma [D][K], host.               */
+int oni_lda_save_model(const char *root, int32_t num_topics, int32_t num_terms,
+                       const double *logbeta, double alpha);
+int oni_lda_save_gamma(const char *path, int32_t num_docs, int32_t num_topics,
+                       const double *gamma);
+
+/* ------------------------------------------------------------------------ */
+/* Post-LDA event scoring (flow_post_lda.scala:227-245,                      */
+/* dns_post_lda.scala:312-326).                                               */
+/* theta [D][K] and pwz [V][K] (word-major) are the tables lda_post.py writes */
+/* (doc_results.csv / word_results.csv, lda_post.py:35-59,70-122).  Events    */
+/* carry integer indices; index < 0 = lookup miss -> the constant vector      */
+/* (0.05 flow, 0.1 DNS).  Score = sum_{i<K} theta[i]*p[i] with one rounded    */
+/* multiply and one rounded add per term (JVM semantics, no FMA).             */
+/* Survivors (key < tol, strict) come back ascending by key, ties by event    */
+/* index.  out_idx/out_key have room for out_cap entries; *out_n is the total */
+/* number of survivors (may exceed out_cap; then only the first out_cap       */
+/* ranked entries are written).  out_src_score / out_dst_score receive the    */
+/* two per-side scores of the ranked survivors.  All pointers are HOST memory. */
+int oni_score_flow(int32_t device, int32_t num_topics, int32_t num_docs, int32_t num_terms,
+                   const double *theta, const double *pwz, int64_t num_events,
+                   const int32_t *src_doc, const int32_t *dst_doc, const int32_t *src_word,
+                   const int32_t *dst_word, double tol, int64_t out_cap, int64_t *out_idx,
+                   double *out_key, double *out_src_score /* [out_cap], ranked; may be NULL */,
+                   double *out_dst_score /* [out_cap], ranked; may be NULL */, int64_t *out_n);
+int oni_score_dns(int32_t device, int32_t num_topics, int32_t num_docs, int32_t num_terms,
+                  const double *theta, const double *pwz, int64_t num_events,
+                  const int32_t *doc, const int32_t *word, double tol, int64_t out_cap,
+                  int64_t *out_idx, double *out_key, int64_t *out_n);
+
+/* The same path with the event indices already on the device (what the host  */
+/* entry points above are built on; a day of events is pushed chunk by chunk). */
+typedef struct oni_score_ctx oni_score_ctx;
+/* Uploads theta [D][K] and pwz [V][K] (host). */
+int oni_score_create(int32_t device, int32_t num_topics, int32_t num_docs, int32_t num_terms,
+                     const double *theta, const double *pwz, oni_score_ctx **out);
+void oni_score_destroy(oni_score_ctx *ctx);
+/* Empty the survivor list. */
+int oni_score_begin(oni_score_ctx *ctx);
+/* Score `num_events` events (device index arrays; b_* ignored for DNS) and     */
+/* append those with key < tol; idx_base = global index of the first event.   */
+int oni_score_events_device(oni_score_ctx *ctx, int32_t is_flow, int64_t num_events,
+                            int64_t idx_base, const int32_t *a_doc, const int32_t *b_doc,
+                            const int32_t *a_word, const int32_t *b_word, double tol);
+/* Rank the survivors: ascending key, ties by event index. */
+int oni_score_rank(oni_score_ctx *ctx, int64_t *n_survivors);
+/* First `cap` ranked survivors to host arrays. */
+int oni_score_fetch(oni_score_ctx *ctx, int64_t cap, int64_t *out_idx, double *out_key);
+/* src / dst score of the first `cap` ranked survivors (the two columns the    */
+/* Scala stage appends, flow_post_lda.scala:238); event arrays as above.       */
+int oni_score_fetch_sides(oni_score_ctx *ctx, int32_t is_flow, int64_t cap, int64_t idx_base,
+                          const int32_t *a_doc, const int32_t *b_doc, const int32_t *a_word,
+                          const int32_t *b_word, double *out_a, double *out_b);
+/* CUDA-event times of the last run and kernels launched so far. */
+int oni_score_get_stats(oni_score_ctx *ctx, double *ms_score, double *ms_sort, int64_t *launches);
+
+/* Result shaping of lda_post.py on the device: theta = gamma/sum(gamma)
+ * (lda_post.py:44-54) and pwz = exp(beta)/sum_w exp(beta) (lda_post.py:88-96),
+ * both passed through 12-significant-digit decimal text when text_digits = 12
+ * (0 = keep full doubles).  gamma [D][K], logbeta [K][V], host; outputs host. */
+int oni_lda_post(int32_t device, int32_t num_docs, int32_t num_topics, int32_t num_terms,
+                 const double *gamma, const double *logbeta, int32_t text_digits,
+                 double *theta /* [D][K] */, double *pwz /* [V][K] */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ONI_LDA_H */

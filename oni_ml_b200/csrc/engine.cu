@@ -1,0 +1,756 @@
+// engine.cu -- the step-wise LDA engine behind include/oni_lda.h: one context per
+// GPU holding a shard of the documents, the replicated model and the packed
+// sufficient statistics.  Replaces run_em (oni-lda-c/lda-estimate.c:112-321).
+//
+// HBM layout of a context (D docs, NNZ pairs in the shard, V terms, K topics,
+// KP = K rounded up to 4 so every row starts on a 32-byte boundary):
+//   tok        int2   [NNZ]      (word, count) of each pair, document order
+//   doc_ptr    int64  [D+1]
+//   order      int32  [D]        documents, longest first (schedule only)
+//   doc_total  double [D]        sum of counts
+//   perm       int32  [NNZ]      pair ids sorted by word id (stable)
+//   items/items2                 chunk lists of the deterministic reduction
+//   logbeta_t  double [V][KP]    word-major log p(w|k): one row per word visit
+//   phi        double [NNZ][KP]  variational phi; read+written every sweep
+//   gamma      double [D][K]
+//   doc_lik/doc_ass double [D], doc_iters int32 [D]
+//   ss         double [V*KP + KP + 4]  class_word | class_total | tail
+//   partial    double [n_partial][KP]  scratch of the reduction's level 1
+#include <dlfcn.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include <algorithm>
+#include <numeric>
+#include <vector>
+
+#include "common.h"
+#include "estep_launch.h"
+#include "mt19937.h"
+#include "suffstats.cuh"
+
+using namespace oni;
+
+// ----------------------------------------------------------------- NCCL, lazily
+// The library must load on hosts without NCCL (single-GPU use), so the few
+// entry points are resolved with dlopen on first use.
+namespace {
+typedef struct ncclComm *ncclComm_t;
+typedef struct { char internal[ONI_NCCL_ID_BYTES]; } ncclUniqueId;
+enum { kNcclSum = 0, kNcclFloat64 = 8 };
+struct NcclApi {
+    void *handle = nullptr;
+    int (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    int (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+
+int nccl_load()
+{
+    if (g_nccl.handle) return ONI_OK;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    void *h = nullptr;
+    for (const char *n : names) {
+        h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (h) break;
+    }
+    if (!h) return oni_set_error(ONI_ERR_NCCL, "cannot load libnccl: %s", dlerror());
+#define ONI_SYM(field, sym)                                                         \
+    *(void **)(&g_nccl.field) = dlsym(h, sym);                                      \
+    if (!g_nccl.field) return oni_set_error(ONI_ERR_NCCL, "libnccl lacks %s", sym);
+    ONI_SYM(GetUniqueId, "ncclGetUniqueId")
+    ONI_SYM(CommInitRank, "ncclCommInitRank")
+    ONI_SYM(CommInitAll, "ncclCommInitAll")
+    ONI_SYM(CommDestroy, "ncclCommDestroy")
+    ONI_SYM(AllReduce, "ncclAllReduce")
+    ONI_SYM(GroupStart, "ncclGroupStart")
+    ONI_SYM(GroupEnd, "ncclGroupEnd")
+    ONI_SYM(GetErrorString, "ncclGetErrorString")
+#undef ONI_SYM
+    g_nccl.handle = h;
+    return ONI_OK;
+}
+#define ONI_NCCL(call)                                                              \
+    do {                                                                            \
+        int r_ = (call);                                                            \
+        if (r_ != 0)                                                                \
+            return oni_set_error(ONI_ERR_NCCL, "%s failed: %s", #call,              \
+                                 g_nccl.GetErrorString(r_));                        \
+    } while (0)
+}  // namespace
+
+// ------------------------------------------------------------------ the context
+struct oni_lda_ctx {
+    int device = 0;
+    int K = 0, KP = 0, V = 0, G = 0, T = 0;
+    oni_lda_settings st{};
+    int var_max_iter = 0;  // doubles when the bound decreases (lda-estimate.c:261)
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6] = {};
+    int sm_count = 0;
+
+    // corpus shard
+    int D = 0;
+    int64_t nnz = 0;
+    int2 *d_tok = nullptr;
+    int64_t *d_doc_ptr = nullptr;
+    int32_t *d_order = nullptr;
+    double *d_doc_total = nullptr;
+    int32_t *d_perm = nullptr;
+    SsItem *d_items = nullptr, *d_items2 = nullptr;
+    int32_t n_items = 0, n_items2 = 0, n_partial = 0;
+
+    // model + variational state
+    double *d_logbeta_t = nullptr, *d_alpha = nullptr;
+    double *d_phi = nullptr, *d_gamma = nullptr, *d_doc_lik = nullptr, *d_doc_ass = nullptr;
+    int32_t *d_doc_iters = nullptr;
+    double *d_ss = nullptr, *d_partial = nullptr, *d_block_partial = nullptr;
+    unsigned int *d_ticket = nullptr, *d_done = nullptr;
+    int32_t *d_nan = nullptr;
+    double *h_pinned = nullptr;  // [8] tail + alpha + nan flag readback
+
+    // EM bookkeeping (lda-estimate.c:174-176)
+    int em_iter = 0;
+    double alpha = 0.0, lik_old = 0.0, converged = 1.0;
+    bool have_model = false, estep_done = false;
+
+    ncclComm_t comm = nullptr;
+    int nranks = 1;
+    int64_t launches = 0;
+    oni_lda_stats stats{};
+
+    size_t ss_count() const { return (size_t)V * KP + KP + 4; }
+    double *ss_class_total() const { return d_ss + (size_t)V * KP; }
+    double *ss_tail() const { return d_ss + (size_t)V * KP + KP; }
+};
+
+namespace {
+
+// lanes per document (G) and topics per lane (T): fewest padded slots with
+// T <= 8, ties to the smaller G (fewer shuffle steps).
+bool pick_config(int K, int *G, int *T)
+{
+    // instantiated: G = 1 with T = 1..8, and G in {2,4,8,16,32} with T = 5..8
+    int best_g = 0, best_t = 0, best_slots = 1 << 30;
+    for (int g = 1; g <= 32; g <<= 1) {
+        const int t = (K + g - 1) / g;
+        if (t > 8 || (g > 1 && t < 5)) continue;
+        if (g * t < best_slots) { best_slots = g * t; best_g = g; best_t = t; }
+    }
+    if (!best_g) return false;
+    *G = best_g; *T = best_t;
+    return true;
+}
+
+template <typename Tp>
+int dev_alloc(Tp **p, size_t n)
+{
+    ONI_CUDA(cudaMalloc((void **)p, sizeof(Tp) * (n ? n : 1)));
+    return ONI_OK;
+}
+
+void free_corpus(oni_lda_ctx *c)
+{
+    cudaFree(c->d_tok); cudaFree(c->d_doc_ptr); cudaFree(c->d_order); cudaFree(c->d_doc_total);
+    cudaFree(c->d_perm); cudaFree(c->d_items); cudaFree(c->d_items2); cudaFree(c->d_phi);
+    cudaFree(c->d_gamma); cudaFree(c->d_doc_lik); cudaFree(c->d_doc_ass); cudaFree(c->d_doc_iters);
+    cudaFree(c->d_partial);
+    c->d_tok = nullptr; c->d_doc_ptr = nullptr; c->d_order = nullptr; c->d_doc_total = nullptr;
+    c->d_perm = nullptr; c->d_items = c->d_items2 = nullptr; c->d_phi = nullptr;
+    c->d_gamma = c->d_doc_lik = c->d_doc_ass = nullptr; c->d_doc_iters = nullptr;
+    c->d_partial = nullptr;
+    c->D = 0; c->nnz = 0;
+}
+
+// Host-side, once per corpus: schedule order, word-sorted pair index, chunk lists.
+int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *ptr, const int32_t *word,
+                  const int32_t *count)
+{
+    if (nnz > 0x7fffffffLL)
+        return oni_set_error(ONI_ERR_ARG, "shard has %lld pairs; at most 2^31-1 per GPU", (long long)nnz);
+    const int V = c->V;
+    for (int64_t i = 0; i < nnz; i++)
+        if (word[i] < 0 || word[i] >= V)
+            return oni_set_error(ONI_ERR_ARG, "word id %d outside [0,%d)", word[i], V);
+    for (int32_t d = 0; d < D; d++)
+        if (ptr[d + 1] < ptr[d]) return oni_set_error(ONI_ERR_ARG, "doc_ptr not monotone at %d", d);
+    if (ptr[0] != 0 || ptr[D] != nnz) return oni_set_error(ONI_ERR_ARG, "doc_ptr does not span the pairs");
+
+    std::vector<int2> tok((size_t)nnz);
+    for (int64_t i = 0; i < nnz; i++) tok[i] = make_int2(word[i], count[i]);
+    std::vector<double> total((size_t)D);
+    std::vector<int32_t> order((size_t)D);
+    for (int32_t d = 0; d < D; d++) {
+        int32_t t = 0;  // the reference sums counts in an int (lda.h:27, lda-data.c:47)
+        for (int64_t i = ptr[d]; i < ptr[d + 1]; i++) t += count[i];
+        total[d] = (double)t;
+        order[d] = d;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
+        return (ptr[a + 1] - ptr[a]) > (ptr[b + 1] - ptr[b]);
+    });
+
+    // counting sort of pair ids by word (stable: document order inside a word)
+    std::vector<int64_t> wptr((size_t)V + 1, 0);
+    for (int64_t i = 0; i < nnz; i++) wptr[word[i] + 1]++;
+    for (int w = 0; w < V; w++) wptr[w + 1] += wptr[w];
+    std::vector<int32_t> perm((size_t)nnz);
+    {
+        std::vector<int64_t> cur(wptr.begin(), wptr.end() - 1);
+        for (int64_t i = 0; i < nnz; i++) perm[cur[word[i]]++] = (int32_t)i;
+    }
+    // chunk lists
+    std::vector<SsItem> items, items2;
+    int32_t n_partial = 0;
+    for (int w = 0; w < V; w++) {
+        const int64_t a = wptr[w], n = wptr[w + 1] - a;
+        if (n <= SS_CHUNK) {
+            items.push_back(SsItem{a, (int32_t)n, w});
+        } else {
+            const int32_t first = n_partial;
+            for (int64_t o = 0; o < n; o += SS_CHUNK) {
+                items.push_back(SsItem{a + o, (int32_t)std::min<int64_t>(SS_CHUNK, n - o), ~n_partial});
+                n_partial++;
+            }
+            items2.push_back(SsItem{first, n_partial - first, w});
+        }
+    }
+
+    free_corpus(c);
+    c->D = D; c->nnz = nnz;
+    c->n_items = (int32_t)items.size(); c->n_items2 = (int32_t)items2.size(); c->n_partial = n_partial;
+    ONI_TRY(dev_alloc(&c->d_tok, (size_t)nnz));
+    ONI_TRY(dev_alloc(&c->d_doc_ptr, (size_t)D + 1));
+    ONI_TRY(dev_alloc(&c->d_order, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_doc_total, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_perm, (size_t)nnz));
+    ONI_TRY(dev_alloc(&c->d_items, items.size()));
+    ONI_TRY(dev_alloc(&c->d_items2, items2.size()));
+    ONI_TRY(dev_alloc(&c->d_phi, (size_t)nnz * c->KP));
+    ONI_TRY(dev_alloc(&c->d_gamma, (size_t)D * c->K));
+    ONI_TRY(dev_alloc(&c->d_doc_lik, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_doc_ass, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_doc_iters, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_partial, (size_t)n_partial * c->KP));
+    cudaStream_t s = c->stream;
+    ONI_CUDA(cudaMemcpyAsync(c->d_tok, tok.data(), sizeof(int2) * (size_t)nnz, cudaMemcpyHostToDevice, s));
+    ONI_CUDA(cudaMemcpyAsync(c->d_doc_ptr, ptr, sizeof(int64_t) * ((size_t)D + 1), cudaMemcpyHostToDevice, s));
+    ONI_CUDA(cudaMemcpyAsync(c->d_order, order.data(), sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, s));
+    ONI_CUDA(cudaMemcpyAsync(c->d_doc_total, total.data(), sizeof(double) * (size_t)D, cudaMemcpyHostToDevice, s));
+    ONI_CUDA(cudaMemcpyAsync(c->d_perm, perm.data(), sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, s));
+    ONI_CUDA(cudaMemcpyAsync(c->d_items, items.data(), sizeof(SsItem) * items.size(), cudaMemcpyHostToDevice, s));
+    ONI_CUDA(cudaMemcpyAsync(c->d_items2, items2.data(), sizeof(SsItem) * items2.size(), cudaMemcpyHostToDevice, s));
+    ONI_CUDA(cudaMemsetAsync(c->d_gamma, 0, sizeof(double) * (size_t)D * c->K, s));
+    ONI_CUDA(cudaMemsetAsync(c->d_doc_iters, 0, sizeof(int32_t) * (size_t)D, s));
+    ONI_CUDA(cudaStreamSynchronize(s));  // host vectors die at return
+    return ONI_OK;
+}
+
+template <int G, int T>
+void launch_ss(oni_lda_ctx *c)
+{
+    const int warps_per_block = 4;
+    if (c->n_items > 0) {
+        const int blocks = (c->n_items + warps_per_block - 1) / warps_per_block;
+        ss_rows_kernel<G, T, 1><<<blocks, 128, 0, c->stream>>>(
+            c->d_items, c->n_items, c->d_perm, c->d_tok, c->d_phi, c->d_ss, c->d_partial, c->K, c->KP);
+        c->launches++;
+    }
+    if (c->n_items2 > 0) {
+        const int blocks = (c->n_items2 + warps_per_block - 1) / warps_per_block;
+        ss_rows_kernel<G, T, 2><<<blocks, 128, 0, c->stream>>>(
+            c->d_items2, c->n_items2, nullptr, nullptr, c->d_partial, c->d_ss, c->d_partial, c->K, c->KP);
+        c->launches++;
+    }
+}
+
+int dispatch_ss(oni_lda_ctx *c)
+{
+#define ONI_SS_CASE(G_, T_) \
+    if (c->G == G_ && c->T == T_) { launch_ss<G_, T_>(c); return ONI_OK; }
+#define ONI_SS_T58(G_) ONI_SS_CASE(G_, 5) ONI_SS_CASE(G_, 6) ONI_SS_CASE(G_, 7) ONI_SS_CASE(G_, 8)
+    ONI_SS_CASE(1, 1) ONI_SS_CASE(1, 2) ONI_SS_CASE(1, 3) ONI_SS_CASE(1, 4)
+    ONI_SS_T58(1) ONI_SS_T58(2) ONI_SS_T58(4) ONI_SS_T58(8) ONI_SS_T58(16) ONI_SS_T58(32)
+#undef ONI_SS_T58
+#undef ONI_SS_CASE
+    return oni_set_error(ONI_ERR_ARG, "no reduction kernel for G=%d T=%d", c->G, c->T);
+}
+
+double now_seconds()
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec + 1e-9 * ts.tv_nsec;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------- lifecycle
+extern "C" int oni_lda_create(int32_t device, int32_t K, int32_t V, const oni_lda_settings *st,
+                              oni_lda_ctx **out)
+{
+    if (!out || !st) return oni_set_error(ONI_ERR_ARG, "create: null argument");
+    *out = nullptr;
+    if (K < 1 || V < 1) return oni_set_error(ONI_ERR_ARG, "create: num_topics=%d num_terms=%d", K, V);
+    int G, T;
+    if (!pick_config(K, &G, &T))
+        return oni_set_error(ONI_ERR_ARG, "num_topics=%d not supported (1..256)", K);
+    if (st->var_max_iter == 0)
+        return oni_set_error(ONI_ERR_ARG, "var max iter 0 is not supported (use -1 for no cap)");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return oni_set_error(ONI_ERR_CUDA, "no CUDA device: this engine has no CPU path");
+    if (device < 0 || device >= ndev)
+        return oni_set_error(ONI_ERR_ARG, "device %d of %d", device, ndev);
+    ONI_CUDA(cudaSetDevice(device));
+    oni_lda_ctx *c = new oni_lda_ctx();
+    c->device = device; c->K = K; c->KP = (K + 3) & ~3; c->V = V; c->G = G; c->T = T;
+    c->st = *st; c->var_max_iter = st->var_max_iter;
+    cudaDeviceProp prop;
+    ONI_CUDA(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    ONI_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (auto &e : c->ev) ONI_CUDA(cudaEventCreate(&e));
+    ONI_TRY(dev_alloc(&c->d_logbeta_t, (size_t)V * c->KP));
+    ONI_TRY(dev_alloc(&c->d_alpha, 1));
+    ONI_TRY(dev_alloc(&c->d_ss, c->ss_count()));
+    ONI_TRY(dev_alloc(&c->d_block_partial, (size_t)DOC_RED_BLOCKS * 3));
+    ONI_TRY(dev_alloc(&c->d_ticket, 1));
+    ONI_TRY(dev_alloc(&c->d_done, 1));
+    ONI_TRY(dev_alloc(&c->d_nan, 1));
+    ONI_CUDA(cudaMemset(c->d_done, 0, sizeof(unsigned)));
+    ONI_CUDA(cudaMemset(c->d_nan, 0, sizeof(int32_t)));
+    ONI_CUDA(cudaMemset(c->d_ss, 0, sizeof(double) * c->ss_count()));
+    ONI_CUDA(cudaMallocHost((void **)&c->h_pinned, sizeof(double) * 8));
+    *out = c;
+    return ONI_OK;
+}
+
+extern "C" void oni_lda_destroy(oni_lda_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    free_corpus(c);
+    cudaFree(c->d_logbeta_t); cudaFree(c->d_alpha); cudaFree(c->d_ss); cudaFree(c->d_block_partial);
+    cudaFree(c->d_ticket); cudaFree(c->d_done); cudaFree(c->d_nan);
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    for (auto &e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" int oni_lda_set_corpus(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *ptr,
+                                  const int32_t *word, const int32_t *count)
+{
+    if (!c || !ptr || (nnz > 0 && (!word || !count)) || D < 0 || nnz < 0)
+        return oni_set_error(ONI_ERR_ARG, "set_corpus: bad argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    c->estep_done = false;
+    return build_indices(c, D, nnz, ptr, word, count);
+}
+
+extern "C" int oni_lda_set_corpus_device(oni_lda_ctx *c, int32_t D, int64_t nnz,
+                                         const int64_t *d_ptr, const int32_t *d_word,
+                                         const int32_t *d_count)
+{
+    if (!c || !d_ptr || D < 0 || nnz < 0) return oni_set_error(ONI_ERR_ARG, "set_corpus_device: bad argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    std::vector<int64_t> ptr((size_t)D + 1);
+    std::vector<int32_t> word((size_t)nnz), count((size_t)nnz);
+    ONI_CUDA(cudaMemcpy(ptr.data(), d_ptr, sizeof(int64_t) * ((size_t)D + 1), cudaMemcpyDeviceToHost));
+    if (nnz) {
+        ONI_CUDA(cudaMemcpy(word.data(), d_word, sizeof(int32_t) * (size_t)nnz, cudaMemcpyDeviceToHost));
+        ONI_CUDA(cudaMemcpy(count.data(), d_count, sizeof(int32_t) * (size_t)nnz, cudaMemcpyDeviceToHost));
+    }
+    c->estep_done = false;
+    return build_indices(c, D, nnz, ptr.data(), word.data(), count.data());
+}
+
+// Upload a topic-major host model into the word-major device table.
+static int upload_model(oni_lda_ctx *c, const double *logbeta, double alpha)
+{
+    std::vector<double> t((size_t)c->V * c->KP, 0.0);
+    for (int k = 0; k < c->K; k++)
+        for (int w = 0; w < c->V; w++) t[(size_t)w * c->KP + k] = logbeta[(size_t)k * c->V + w];
+    ONI_CUDA(cudaMemcpy(c->d_logbeta_t, t.data(), sizeof(double) * t.size(), cudaMemcpyHostToDevice));
+    ONI_CUDA(cudaMemcpy(c->d_alpha, &alpha, sizeof(double), cudaMemcpyHostToDevice));
+    c->alpha = alpha;
+    c->have_model = true;
+    c->em_iter = 0; c->lik_old = 0.0; c->converged = 1.0;
+    c->var_max_iter = c->st.var_max_iter;
+    return ONI_OK;
+}
+
+// random_initialize_ss + lda_mle(model, ss, 0) on the host with the reference's
+// stream and libm, so 000.beta is byte-identical (lda-model.c:104-117,27-44).
+void oni_internal_random_model(int K, int V, uint32_t seed, std::vector<double> &logbeta)
+{
+    CokusMT mt(seed);
+    logbeta.assign((size_t)K * V, 0.0);
+    std::vector<double> cw((size_t)V);
+    for (int k = 0; k < K; k++) {
+        double ct = 0.0;
+        for (int n = 0; n < V; n++) {
+            cw[n] = 1.0 / V + mt.uniform();
+            ct += cw[n];
+        }
+        const double lct = log(ct);
+        for (int n = 0; n < V; n++)
+            logbeta[(size_t)k * V + n] = (cw[n] > 0) ? log(cw[n]) - lct : -100.0;
+    }
+}
+
+extern "C" int oni_lda_init_random(oni_lda_ctx *c, uint32_t seed, double alpha)
+{
+    if (!c) return oni_set_error(ONI_ERR_ARG, "init_random: null context");
+    ONI_CUDA(cudaSetDevice(c->device));
+    std::vector<double> lb;
+    oni_internal_random_model(c->K, c->V, seed, lb);
+    return upload_model(c, lb.data(), alpha);
+}
+
+extern "C" int oni_lda_set_model(oni_lda_ctx *c, const double *logbeta, double alpha)
+{
+    if (!c || !logbeta) return oni_set_error(ONI_ERR_ARG, "set_model: null argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    return upload_model(c, logbeta, alpha);
+}
+
+// ------------------------------------------------------------------------ steps
+extern "C" int oni_lda_e_step(oni_lda_ctx *c)
+{
+    if (!c) return oni_set_error(ONI_ERR_ARG, "e_step: null context");
+    if (!c->have_model) return oni_set_error(ONI_ERR_ARG, "e_step: no model (init_random / set_model first)");
+    if (!c->d_doc_ptr) return oni_set_error(ONI_ERR_ARG, "e_step: no corpus");
+    ONI_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+
+    EstepParams p{};
+    p.tok = c->d_tok; p.doc_ptr = c->d_doc_ptr; p.order = c->d_order; p.doc_total = c->d_doc_total;
+    p.logbeta_t = c->d_logbeta_t; p.phi = c->d_phi; p.gamma = c->d_gamma; p.doc_lik = c->d_doc_lik;
+    p.doc_ass = c->d_doc_ass; p.doc_iters = c->d_doc_iters; p.alpha = c->d_alpha;
+    p.ticket = c->d_ticket; p.nan_flag = c->d_nan;
+    p.D = c->D; p.K = c->K; p.KP = c->KP;
+    p.var_max_iter = c->var_max_iter;
+    p.var_converged = (double)c->st.var_converged;  // float promoted, lda-inference.c:46
+
+    // exp(x) cannot underflow for every topic of a word unless digamma(alpha)
+    // is hugely negative, i.e. alpha tiny; then use the max-shifted kernel.
+    const bool shift = !(c->alpha > 0.01);
+
+    ONI_CUDA(cudaMemsetAsync(c->d_ticket, 0, sizeof(unsigned), s));
+    ONI_CUDA(cudaEventRecord(c->ev[0], s));
+    if (c->D > 0) {
+        cudaError_t e = launch_estep(c->G, c->T, shift, p, c->sm_count, s);
+        if (e != cudaSuccess)
+            return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=%d,T=%d): %s", c->G, c->T, cudaGetErrorString(e));
+        c->launches++;
+    }
+    ONI_CUDA(cudaEventRecord(c->ev[1], s));
+    ONI_TRY(dispatch_ss(c));
+    {
+        int S = 1;
+        while (S * 2 * c->KP <= 1024) S *= 2;
+        class_total_kernel<<<1, S * c->KP, sizeof(double) * S * c->KP, s>>>(c->d_ss, c->V, c->K, c->KP,
+                                                                           c->ss_class_total());
+        doc_reduce_kernel<<<DOC_RED_BLOCKS, DOC_RED_THREADS, 0, s>>>(
+            c->d_doc_lik, c->d_doc_ass, c->d_doc_iters, c->d_doc_ptr, c->D, c->d_block_partial, c->d_done,
+            c->ss_tail());
+        c->launches += 2;
+    }
+    ONI_CUDA(cudaEventRecord(c->ev[2], s));
+    ONI_CUDA(cudaGetLastError());
+    c->estep_done = true;
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_suffstats(oni_lda_ctx *c, double **d_buffer, size_t *count)
+{
+    if (!c) return oni_set_error(ONI_ERR_ARG, "suffstats: null context");
+    if (d_buffer) *d_buffer = c->d_ss;
+    if (count) *count = c->ss_count();
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_comm_unique_id(unsigned char id[ONI_NCCL_ID_BYTES])
+{
+    ONI_TRY(nccl_load());
+    ncclUniqueId u;
+    ONI_NCCL(g_nccl.GetUniqueId(&u));
+    memcpy(id, u.internal, ONI_NCCL_ID_BYTES);
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_comm_init(oni_lda_ctx *c, const unsigned char id[ONI_NCCL_ID_BYTES],
+                                 int32_t rank, int32_t nranks)
+{
+    if (!c || !id || nranks < 1 || rank < 0 || rank >= nranks)
+        return oni_set_error(ONI_ERR_ARG, "comm_init: bad argument");
+    ONI_TRY(nccl_load());
+    ONI_CUDA(cudaSetDevice(c->device));
+    ncclUniqueId u;
+    memcpy(u.internal, id, ONI_NCCL_ID_BYTES);
+    ONI_NCCL(g_nccl.CommInitRank(&c->comm, nranks, u, rank));
+    c->nranks = nranks;
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_allreduce(oni_lda_ctx *c)
+{
+    if (!c) return oni_set_error(ONI_ERR_ARG, "allreduce: null context");
+    if (!c->comm || c->nranks == 1) return ONI_OK;
+    ONI_CUDA(cudaSetDevice(c->device));
+    // one collective for what the reference does with 2K+3 (lda-estimate.c:211-252)
+    ONI_NCCL(g_nccl.AllReduce(c->d_ss, c->d_ss, c->ss_count(), kNcclFloat64, kNcclSum, c->comm, c->stream));
+    return ONI_OK;
+}
+
+// M-step kernels only (asynchronous); finish_m_step reads the scalars back.
+static int launch_m_step(oni_lda_ctx *c)
+{
+    cudaStream_t s = c->stream;
+    ONI_CUDA(cudaEventRecord(c->ev[3], s));
+    const size_t n = (size_t)c->V * c->KP;
+    const int blocks = (int)std::min<size_t>((n + 255) / 256, (size_t)c->sm_count * 8);
+    mle_beta_kernel<<<blocks, 256, 0, s>>>(c->d_ss, c->ss_class_total(), c->V, c->K, c->KP, c->d_logbeta_t);
+    c->launches++;
+    if (c->st.estimate_alpha == 1) {  // lda-model.c:46-53
+        alpha_newton_kernel<<<1, 32, 0, s>>>(c->ss_tail(), c->K, c->d_alpha);
+        c->launches++;
+    }
+    ONI_CUDA(cudaEventRecord(c->ev[4], s));
+    ONI_CUDA(cudaMemcpyAsync(c->h_pinned, c->ss_tail(), sizeof(double) * 4, cudaMemcpyDeviceToHost, s));
+    ONI_CUDA(cudaMemcpyAsync(c->h_pinned + 4, c->d_alpha, sizeof(double), cudaMemcpyDeviceToHost, s));
+    ONI_CUDA(cudaMemcpyAsync(c->h_pinned + 5, c->d_nan, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    return ONI_OK;
+}
+
+static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
+{
+    ONI_CUDA(cudaStreamSynchronize(c->stream));
+    int32_t nan_flag;
+    memcpy(&nan_flag, c->h_pinned + 5, sizeof nan_flag);
+    const double lik = c->h_pinned[1];
+    c->alpha = c->h_pinned[4];
+    c->stats.word_visits = (int64_t)c->h_pinned[3];
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) c->stats.ms_estep_kernel = ms;
+    if (cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]) == cudaSuccess) c->stats.ms_suffstats = ms;
+    if (cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]) == cudaSuccess) c->stats.ms_mstep = ms;
+    c->stats.kernel_launches = c->launches;
+    if (nan_flag || lik != lik)
+        return oni_set_error(ONI_ERR_NAN, "a document bound is NaN (EM iteration %d)", c->em_iter + 1);
+    // lda-estimate.c:260-262
+    c->em_iter++;
+    c->converged = (c->lik_old - lik) / c->lik_old;
+    if (c->converged < 0 && c->var_max_iter > 0) c->var_max_iter *= 2;
+    c->lik_old = lik;
+    c->estep_done = false;
+    if (likelihood) *likelihood = lik;
+    if (converged) *converged = c->converged;
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
+{
+    if (!c) return oni_set_error(ONI_ERR_ARG, "m_step: null context");
+    if (!c->estep_done) return oni_set_error(ONI_ERR_ARG, "m_step: no E-step since the last M-step");
+    ONI_CUDA(cudaSetDevice(c->device));
+    ONI_TRY(launch_m_step(c));
+    return finish_m_step(c, likelihood, converged);
+}
+
+extern "C" int oni_lda_em_iteration(oni_lda_ctx *c, double *likelihood, double *converged)
+{
+    ONI_TRY(oni_lda_e_step(c));
+    ONI_TRY(oni_lda_allreduce(c));
+    return oni_lda_m_step(c, likelihood, converged);
+}
+
+extern "C" int oni_lda_em_should_continue(const oni_lda_ctx *c)
+{
+    if (!c) return 0;
+    // lda-estimate.c:186
+    const double em_conv = (double)c->st.em_converged;
+    return (((c->converged < 0) || (c->converged > em_conv) || (c->em_iter <= 2)) &&
+            (c->em_iter <= c->st.em_max_iter)) ? 1 : 0;
+}
+
+// --------------------------------------------------------------------- readback
+extern "C" int oni_lda_get_logbeta(oni_lda_ctx *c, double *logbeta)
+{
+    if (!c || !logbeta) return oni_set_error(ONI_ERR_ARG, "get_logbeta: null argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    std::vector<double> t((size_t)c->V * c->KP);
+    ONI_CUDA(cudaStreamSynchronize(c->stream));
+    ONI_CUDA(cudaMemcpy(t.data(), c->d_logbeta_t, sizeof(double) * t.size(), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < c->K; k++)
+        for (int w = 0; w < c->V; w++) logbeta[(size_t)k * c->V + w] = t[(size_t)w * c->KP + k];
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_get_gamma(oni_lda_ctx *c, double *gamma)
+{
+    if (!c || !gamma) return oni_set_error(ONI_ERR_ARG, "get_gamma: null argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    ONI_CUDA(cudaStreamSynchronize(c->stream));
+    ONI_CUDA(cudaMemcpy(gamma, c->d_gamma, sizeof(double) * (size_t)c->D * c->K, cudaMemcpyDeviceToHost));
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_get_alpha(oni_lda_ctx *c, double *alpha)
+{
+    if (!c || !alpha) return oni_set_error(ONI_ERR_ARG, "get_alpha: null argument");
+    *alpha = c->alpha;
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_get_doc_likelihood(oni_lda_ctx *c, double *lik)
+{
+    if (!c || !lik) return oni_set_error(ONI_ERR_ARG, "get_doc_likelihood: null argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    ONI_CUDA(cudaStreamSynchronize(c->stream));
+    ONI_CUDA(cudaMemcpy(lik, c->d_doc_lik, sizeof(double) * (size_t)c->D, cudaMemcpyDeviceToHost));
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_get_doc_iters(oni_lda_ctx *c, int32_t *iters)
+{
+    if (!c || !iters) return oni_set_error(ONI_ERR_ARG, "get_doc_iters: null argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    ONI_CUDA(cudaStreamSynchronize(c->stream));
+    ONI_CUDA(cudaMemcpy(iters, c->d_doc_iters, sizeof(int32_t) * (size_t)c->D, cudaMemcpyDeviceToHost));
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_get_stats(oni_lda_ctx *c, oni_lda_stats *out)
+{
+    if (!c || !out) return oni_set_error(ONI_ERR_ARG, "get_stats: null argument");
+    c->stats.kernel_launches = c->launches;
+    *out = c->stats;
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_stream(oni_lda_ctx *c, void **cuda_stream)
+{
+    if (!c || !cuda_stream) return oni_set_error(ONI_ERR_ARG, "stream: null argument");
+    *cuda_stream = (void *)c->stream;
+    return ONI_OK;
+}
+
+// ---------------------------------------------------------- whole-run, in memory
+// Contiguous shards balanced by pair count: cut[r]..cut[r+1].
+static void shard_docs(const oni_lda_corpus *c, int n, std::vector<int32_t> &cut)
+{
+    cut.assign((size_t)n + 1, 0);
+    cut[n] = c->num_docs;
+    for (int r = 1; r < n; r++) {
+        const int64_t target = c->nnz * r / n;
+        const int64_t *it = std::lower_bound(c->doc_ptr, c->doc_ptr + c->num_docs + 1, target);
+        cut[r] = std::max<int32_t>(cut[r - 1], (int32_t)std::min<int64_t>(it - c->doc_ptr, c->num_docs));
+    }
+}
+
+int oni_internal_estimate(const oni_lda_corpus *corpus, int32_t K, double initial_alpha,
+                          const oni_lda_settings *st, const double *logbeta0, int32_t ngpus,
+                          oni_lda_result *res, oni_iter_callback on_iter, void *user)
+{
+    if (!corpus || !st || !res) return oni_set_error(ONI_ERR_ARG, "estimate: null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return oni_set_error(ONI_ERR_CUDA, "no CUDA device: this engine has no CPU path");
+    if (ngpus < 1) ngpus = 1;
+    if (ngpus > ndev)
+        return oni_set_error(ONI_ERR_ARG, "%d GPUs requested, %d visible", ngpus, ndev);
+    const int V = corpus->num_terms, D = corpus->num_docs;
+
+    std::vector<oni_lda_ctx *> ctx((size_t)ngpus, nullptr);
+    std::vector<int32_t> cut;
+    shard_docs(corpus, ngpus, cut);
+    int rc = ONI_OK;
+    auto cleanup = [&]() { for (auto *c : ctx) oni_lda_destroy(c); };
+#define ONI_EST(call) do { rc = (call); if (rc != ONI_OK) { cleanup(); return rc; } } while (0)
+
+    if (res->logbeta_init) memcpy(res->logbeta_init, logbeta0, sizeof(double) * (size_t)K * V);
+
+    for (int r = 0; r < ngpus; r++) {
+        ONI_EST(oni_lda_create(r, K, V, st, &ctx[r]));
+        const int32_t lo = cut[r], hi = cut[r + 1];
+        const int64_t a = corpus->doc_ptr[lo], b = corpus->doc_ptr[hi];
+        std::vector<int64_t> ptr((size_t)(hi - lo) + 1);
+        for (int32_t d = lo; d <= hi; d++) ptr[d - lo] = corpus->doc_ptr[d] - a;
+        ONI_EST(oni_lda_set_corpus(ctx[r], hi - lo, b - a, ptr.data(), corpus->word + a, corpus->count + a));
+        ONI_EST(upload_model(ctx[r], logbeta0, initial_alpha));
+    }
+    if (ngpus > 1) {
+        rc = nccl_load();
+        if (rc != ONI_OK) { cleanup(); return rc; }
+        std::vector<ncclComm_t> comms((size_t)ngpus);
+        std::vector<int> devs((size_t)ngpus);
+        std::iota(devs.begin(), devs.end(), 0);
+        int nr = g_nccl.CommInitAll(comms.data(), ngpus, devs.data());
+        if (nr != 0) { cleanup(); return oni_set_error(ONI_ERR_NCCL, "ncclCommInitAll: %s", g_nccl.GetErrorString(nr)); }
+        for (int r = 0; r < ngpus; r++) { ctx[r]->comm = comms[r]; ctx[r]->nranks = ngpus; }
+    }
+
+    const double t0 = now_seconds();
+    int it = 0;
+    while (oni_lda_em_should_continue(ctx[0])) {
+        for (int r = 0; r < ngpus; r++) ONI_EST(oni_lda_e_step(ctx[r]));
+        if (ngpus > 1) {
+            g_nccl.GroupStart();
+            for (int r = 0; r < ngpus; r++) {
+                rc = oni_lda_allreduce(ctx[r]);
+                if (rc != ONI_OK) break;
+            }
+            g_nccl.GroupEnd();
+            if (rc != ONI_OK) { cleanup(); return rc; }
+        }
+        for (int r = 0; r < ngpus; r++) {
+            rc = cudaSetDevice(ctx[r]->device) == cudaSuccess ? launch_m_step(ctx[r]) : ONI_ERR_CUDA;
+            if (rc != ONI_OK) { cleanup(); return rc; }
+        }
+        double lik = 0, conv = 0;
+        for (int r = 0; r < ngpus; r++) {
+            cudaSetDevice(ctx[r]->device);
+            ONI_EST(finish_m_step(ctx[r], &lik, &conv));
+        }
+        if (it < res->likelihood_cap) {
+            if (res->likelihood) res->likelihood[it] = lik;
+            if (res->converged) res->converged[it] = conv;
+        }
+        it++;
+        if (on_iter) on_iter(user, it, lik, conv);
+    }
+    res->seconds_em = now_seconds() - t0;
+    res->em_iters = it;
+    res->alpha = ctx[0]->alpha;
+    if (res->logbeta) ONI_EST(oni_lda_get_logbeta(ctx[0], res->logbeta));
+    if (res->gamma)
+        for (int r = 0; r < ngpus; r++)
+            ONI_EST(oni_lda_get_gamma(ctx[r], res->gamma + (size_t)cut[r] * K));
+    (void)D;
+    cleanup();
+#undef ONI_EST
+    return ONI_OK;
+}
+
+extern "C" int oni_lda_estimate(const oni_lda_corpus *corpus, int32_t K, double initial_alpha,
+                                const oni_lda_settings *st, uint32_t seed, int32_t ngpus,
+                                oni_lda_result *res)
+{
+    if (!corpus || !st || !res) return oni_set_error(ONI_ERR_ARG, "estimate: null argument");
+    if (K < 1 || corpus->num_terms < 1) return oni_set_error(ONI_ERR_ARG, "estimate: empty model");
+    std::vector<double> lb0;
+    oni_internal_random_model(K, corpus->num_terms, seed, lb0);  // lda-estimate.c:155-161
+    return oni_internal_estimate(corpus, K, initial_alpha, st, lb0.data(), ngpus, res, nullptr, nullptr);
+}

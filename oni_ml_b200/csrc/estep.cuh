@@ -1,0 +1,284 @@
+// estep.cuh -- per-document variational inference (the E-step) on sm_100a.
+//
+// Stands in for lda_inference + compute_likelihood (oni-lda-c/lda-inference.c:
+// 27-127) and the per-document part of doc_e_step (lda-estimate.c:28-46).
+//
+// Mapping.  A document is owned by a GROUP of G adjacent lanes; each lane holds
+// T topics (topic k = j + G*t for lane-in-group j), so a warp runs 32/G
+// documents at once and all 32 lanes carry live topics when G*T == K (K=20:
+// G=4, T=5 -> 8 documents per warp).  Groups pull documents from a global
+// ticket counter in longest-first order; the result of a document does not
+// depend on which group ran it, so the dynamic schedule is deterministic in its
+// outputs.  The document's words are visited strictly in order and gamma /
+// digamma(gamma) are refreshed after every word, exactly like the reference's
+// Gauss-Seidel sweep (lda-inference.c:50-75); only the K-wide work inside one
+// word visit is parallel.
+//
+// Arithmetic (fp64 throughout), restated rather than transliterated:
+//   * phi_nk = exp(x_k) / sum_j exp(x_j), x_k = digamma(gamma_k) + logbeta_kw.
+//     The reference forms log(sum) with a left-to-right log_sum chain
+//     (lda-inference.c:53-64, utils.c:8-21) and then exp(x_k - logsum); the two
+//     agree to a few ulp.  A max-shifted variant (SHIFT) is used when alpha is
+//     so small that exp(x) could underflow for every topic.
+//   * digamma (utils.c:55-64): same asymptotic series and literal coefficients;
+//     the six recurrence terms 1/(x-1)..1/(x-6) = sum_{j<6} 1/(g+j) are folded
+//     into one rational P(g)/Q(g) (one division instead of six).
+//   * the bound (lda-inference.c:93-127).  With S_n = sum_k exp(x_k) at visit n
+//     and psi_k^(n) the digamma values used at that visit,
+//         log phi_nk = psi_k^(n) + logbeta_kw - log S_n ,
+//     and after a full sweep gamma_k - alpha = sum_n c_n phi_nk, so the
+//     (dig_k - digsum) terms of the reference's expression cancel and
+//         L = lgamma(K alpha) - K lgamma(alpha) - lgamma(sum gamma)
+//             + sum_k lgamma(gamma_k)
+//             + sum_n c_n ( log S_n - sum_k phi_nk psi_k^(n) ).
+//     This needs one log per word visit instead of K, and no second sweep over
+//     phi.  Terms with phi == 0 vanish in both forms (the reference skips them,
+//     lda-inference.c:119).
+//   * convergence test and iteration cap exactly as lda-inference.c:46-47,79-80,
+//     including (0 - L)/0 = +inf on the first pass.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace oni {
+
+// ------------------------------------------------------------ special functions
+// Sum_{j=0..5} 1/(g+j) as P(g)/Q(g); all coefficients positive, so Horner on
+// g > 0 has no cancellation.
+__device__ __forceinline__ double recurrence6(double g)
+{
+    double q = g + 15.0;
+    q = fma(q, g, 85.0);
+    q = fma(q, g, 225.0);
+    q = fma(q, g, 274.0);
+    q = fma(q, g, 120.0);
+    q = q * g;
+    double p = fma(6.0, g, 75.0);
+    p = fma(p, g, 340.0);
+    p = fma(p, g, 675.0);
+    p = fma(p, g, 548.0);
+    p = fma(p, g, 120.0);
+    return p / q;
+}
+
+// utils.c:55-64
+__device__ __forceinline__ double dev_digamma(double g)
+{
+    const double x = g + 6.0;
+    const double r = 1.0 / x;
+    const double p = r * r;
+    double ser = fma(0.004166666666667, p, -0.003968253986254);
+    ser = fma(ser, p, 0.008333333333333);
+    ser = fma(ser, p, -0.083333333333333);
+    ser = ser * p;
+    return ((ser + log(x)) - 0.5 * r) - recurrence6(g);
+}
+
+// utils.c:32-47 (only the alpha Newton uses it; kept literal)
+__device__ inline double dev_trigamma(double x)
+{
+    x = x + 6.0;
+    double p = 1.0 / (x * x);
+    p = (((((0.075757575757576 * p - 0.033333333333333) * p + 0.0238095238095238) * p -
+           0.033333333333333) * p + 0.166666666666667) * p + 1.0) / x + 0.5 * p;
+    for (int i = 0; i < 6; i++) {
+        x = x - 1.0;
+        p = 1.0 / (x * x) + p;
+    }
+    return p;
+}
+
+// ------------------------------------------------------------------ parameters
+struct EstepParams {
+    const int2 *tok;           // [NNZ] (word, count)
+    const int64_t *doc_ptr;    // [D+1]
+    const int32_t *order;      // [D] documents, longest first
+    const double *doc_total;   // [D] sum of counts (lda-data.c:47)
+    const double *logbeta_t;   // [V][KP] word-major log p(w|k)
+    double *phi;               // [NNZ][KP]
+    double *gamma;             // [D][K]
+    double *doc_lik;           // [D]
+    double *doc_ass;           // [D] sum_k digamma(gamma_k) - K digamma(sum gamma)
+    int32_t *doc_iters;        // [D]
+    const double *alpha;       // device scalar
+    unsigned int *ticket;      // next position in `order`
+    int32_t *nan_flag;
+    int32_t D, K, KP;
+    int32_t var_max_iter;      // -1 = no cap
+    double var_converged;
+};
+
+template <int G>
+__device__ __forceinline__ double group_sum(double v, unsigned gmask)
+{
+#pragma unroll
+    for (int o = 1; o < G; o <<= 1) v += __shfl_xor_sync(gmask, v, o);
+    return v;
+}
+template <int G>
+__device__ __forceinline__ double group_max(double v, unsigned gmask)
+{
+#pragma unroll
+    for (int o = 1; o < G; o <<= 1) v = fmax(v, __shfl_xor_sync(gmask, v, o));
+    return v;
+}
+
+// ---------------------------------------------------------------- the kernel
+template <int G, int T, bool SHIFT>
+__global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const int j = lane & (G - 1);
+    const int lead = lane & ~(G - 1);
+    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << lead);
+    const int K = p.K, KP = p.KP;
+    const double alpha = *p.alpha;
+    const double inv_k = 1.0 / (double)K;
+    // lda-inference.c:105-108
+    const double lik_const = lgamma(alpha * K) - K * lgamma(alpha);
+
+    bool valid[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) valid[t] = (j + G * t) < K;
+
+    double gam[T], dg[T];
+    double acc_a = 0.0, acc_b = 0.0;  // sum c*phi*psi (this lane's topics), sum c*log S
+    double acc_s = 0.0;               // SHIFT only: sum c*shift (same in every lane)
+    double s_keep = 1.0, c_keep = 0.0;
+    double lik_old = 0.0;
+    int64_t beg = 0, end = 0, pos = 0;
+    int32_t doc = -1, pass = 0;
+    bool have = false, exhausted = false;
+
+    while (true) {
+        if (!have && !exhausted) {
+            unsigned i = 0;
+            if (j == 0) i = atomicAdd(p.ticket, 1u);
+            i = __shfl_sync(gmask, i, lead);
+            if (i >= (unsigned)p.D) {
+                exhausted = true;
+            } else {
+                doc = p.order[i];
+                beg = p.doc_ptr[doc];
+                end = p.doc_ptr[doc + 1];
+                pos = beg;
+                pass = 0;
+                lik_old = 0.0;
+                acc_a = acc_b = acc_s = 0.0;
+                s_keep = 1.0; c_keep = 0.0;
+                // lda-inference.c:37-43
+                const double g0 = alpha + p.doc_total[doc] / ((double)K);
+                const double d0 = dev_digamma(g0);
+#pragma unroll
+                for (int t = 0; t < T; t++) {
+                    gam[t] = valid[t] ? g0 : 1.0;
+                    dg[t] = valid[t] ? d0 : 0.0;
+                }
+                have = true;
+            }
+        }
+        if (__all_sync(0xffffffffu, !have)) break;
+        if (!have) continue;
+
+        if (pos < end) {
+            // ---- one word visit (lda-inference.c:50-75)
+            const int2 tk = __ldg(p.tok + pos);
+            const double c = (double)tk.y;
+            const double *lbrow = p.logbeta_t + (size_t)tk.x * KP;
+            double *phrow = p.phi + (size_t)pos * KP;
+            double x[T], old[T];
+#pragma unroll
+            for (int t = 0; t < T; t++) {
+                const int k = j + G * t;
+                const double lb = valid[t] ? __ldg(lbrow + k) : 0.0;
+                old[t] = valid[t] ? ((pass == 0) ? inv_k : phrow[k]) : 0.0;
+                x[t] = dg[t] + lb;
+            }
+            double shift = 0.0;
+            if (SHIFT) {
+                double m = -1.0e300;
+#pragma unroll
+                for (int t = 0; t < T; t++) m = valid[t] ? fmax(m, x[t]) : m;
+                shift = group_max<G>(m, gmask);
+            }
+            double s = 0.0;
+#pragma unroll
+            for (int t = 0; t < T; t++) {
+                x[t] = valid[t] ? exp(SHIFT ? (x[t] - shift) : x[t]) : 0.0;
+                s += x[t];
+            }
+            s = group_sum<G>(s, gmask);
+            const double rs = 1.0 / s;
+            double a = 0.0;
+#pragma unroll
+            for (int t = 0; t < T; t++) {
+                const int k = j + G * t;
+                const double ph = x[t] * rs;
+                a = fma(ph, dg[t], a);
+                gam[t] = fma(c, ph - old[t], gam[t]);
+                dg[t] = valid[t] ? dev_digamma(gam[t]) : 0.0;
+                if (valid[t]) phrow[k] = ph;
+            }
+            acc_a = fma(c, a, acc_a);
+            if (SHIFT) acc_s = fma(c, shift, acc_s);  // log S_n = shift + log(sum)
+            // log S_n is needed once per visit: lane (n mod G) keeps S_n and the
+            // group takes the logs of G visits in one go.
+            const int slot = (int)(pos - beg) & (G - 1);
+            if (slot == j) { s_keep = s; c_keep = c; }
+            pos++;
+            if (slot == G - 1 || pos == end) {
+                acc_b = fma(c_keep, log(s_keep), acc_b);
+                s_keep = 1.0; c_keep = 0.0;
+            }
+        }
+        if (pos == end) {
+            // ---- end of a sweep: the bound (lda-inference.c:93-127, folded)
+            double gs = 0.0, part = 0.0;
+#pragma unroll
+            for (int t = 0; t < T; t++) {
+                gs += valid[t] ? gam[t] : 0.0;
+                part += valid[t] ? lgamma(gam[t]) : 0.0;
+            }
+            part += acc_b - acc_a;
+#pragma unroll
+            for (int o = 1; o < G; o <<= 1) {
+                gs += __shfl_xor_sync(gmask, gs, o);
+                part += __shfl_xor_sync(gmask, part, o);
+            }
+            const double lik = (lik_const - lgamma(gs)) + part + (SHIFT ? acc_s : 0.0);
+            pass++;
+            // lda-inference.c:79-80 and the loop condition :46-47
+            const double conv = (lik_old - lik) / lik_old;
+            lik_old = lik;
+            bool more = (conv > p.var_converged) &&
+                        ((pass < p.var_max_iter) || (p.var_max_iter == -1));
+            if (lik != lik) {  // assert(!isnan(likelihood)), lda-inference.c:78
+                if (j == 0) atomicExch(p.nan_flag, 1);
+                more = false;
+            }
+            if (more) {
+                pos = beg;
+                acc_a = acc_b = acc_s = 0.0;
+            } else {
+                // ---- document done: gamma row, bound, alpha statistic
+                // (lda-estimate.c:40-46)
+                double ds = 0.0;
+#pragma unroll
+                for (int t = 0; t < T; t++) {
+                    const int k = j + G * t;
+                    ds += valid[t] ? dg[t] : 0.0;
+                    if (valid[t]) p.gamma[(size_t)doc * K + k] = gam[t];
+                }
+                ds = group_sum<G>(ds, gmask);
+                if (j == 0) {
+                    p.doc_lik[doc] = lik;
+                    p.doc_ass[doc] = ds - K * dev_digamma(gs);
+                    p.doc_iters[doc] = pass;
+                }
+                have = false;
+            }
+        }
+    }
+}
+
+}  // namespace oni

@@ -1,0 +1,23 @@
+// estep_launch.h -- dispatch to the E-step instantiation for (G lanes per
+// document, T topics per lane).  Each G lives in its own translation unit
+// (estep_g*.cu) so the build runs them in parallel.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "estep.cuh"
+
+namespace oni {
+
+// Instantiated: G = 1 with T = 1..8; G in {2,4,8,16,32} with T = 5..8.
+// Returns cudaErrorInvalidValue for anything else.
+cudaError_t launch_estep(int G, int T, bool shift, const EstepParams &p, int sm_count,
+                         cudaStream_t stream);
+
+cudaError_t launch_estep_g1(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
+cudaError_t launch_estep_g2(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
+cudaError_t launch_estep_g4(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
+cudaError_t launch_estep_g8(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
+cudaError_t launch_estep_g16(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
+cudaError_t launch_estep_g32(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
+
+}  // namespace oni

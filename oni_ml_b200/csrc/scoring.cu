@@ -1,0 +1,652 @@
+// scoring.cu -- post-LDA event scoring, threshold filter and ranking on sm_100a.
+//
+// Stands in for the scoring loops of flow_post_lda.scala:227-245 and
+// dns_post_lda.scala:312-326, and for the table shaping of lda_post.py.
+//
+//   score kernel   one thread per event: theta row . p(w|z) row with one rounded
+//                  multiply and one rounded add per topic, i = 0..K-1 in order
+//                  (the JVM evaluates `s += a(i)*b(i)` without fusing), flow key
+//                  = min(src, dst); events with key < tol are appended, warp-
+//                  aggregated, to the survivor list (order irrelevant: see sort)
+//   radix sort     stable LSD radix sort, 8-bit digits, over the composite
+//                  (key bits, event index): index digits first, then key digits,
+//                  so equal scores rank by ascending event index and the result
+//                  does not depend on the order survivors were appended in.
+//                  Digit positions where every survivor agrees are skipped.
+//
+// Scratch: survivor keys/indices (two buffers each, ping-pong), per-tile digit
+// counts and their scan.  All of it is global memory owned by the scoring
+// context and sized to the survivor count.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.h"
+
+namespace {
+
+// ------------------------------------------------------------------- score math
+// sum_{i<K} a[i]*b[i], strictly sequential, no contraction.
+__device__ __forceinline__ double dot_rows(const double *__restrict__ a,
+                                           const double *__restrict__ b, int K, bool vec2)
+{
+    double acc = 0.0;
+    if (vec2) {
+        const double2 *a2 = reinterpret_cast<const double2 *>(a);
+        const double2 *b2 = reinterpret_cast<const double2 *>(b);
+        for (int i = 0; i < K / 2; i++) {
+            const double2 x = __ldg(a2 + i), y = __ldg(b2 + i);
+            acc = __dadd_rn(acc, __dmul_rn(x.x, y.x));
+            acc = __dadd_rn(acc, __dmul_rn(x.y, y.y));
+        }
+    } else {
+        for (int i = 0; i < K; i++) acc = __dadd_rn(acc, __dmul_rn(__ldg(a + i), __ldg(b + i)));
+    }
+    return acc;
+}
+
+// One side of an event.  A missing document or word scores with the constant
+// vector (flow_post_lda.scala:228-231, dns_post_lda.scala:313-314).
+__device__ __forceinline__ double side_score(const double *theta, const double *pwz, int K,
+                                             int32_t doc, int32_t word, double dflt, bool vec2)
+{
+    if (doc >= 0 && word >= 0)
+        return dot_rows(theta + (size_t)doc * K, pwz + (size_t)word * K, K, vec2);
+    double acc = 0.0;
+    const double *row = (doc >= 0) ? theta + (size_t)doc * K : (word >= 0 ? pwz + (size_t)word * K : nullptr);
+    for (int i = 0; i < K; i++) {
+        const double other = row ? __ldg(row + i) : dflt;
+        // keep the operand order theta*p of the reference
+        const double prod = (doc >= 0) ? __dmul_rn(other, dflt) : __dmul_rn(dflt, other);
+        acc = __dadd_rn(acc, prod);
+    }
+    return acc;
+}
+
+__device__ __forceinline__ unsigned long long key_bits(double v)
+{
+    unsigned long long u = (unsigned long long)__double_as_longlong(v);
+    return (u >> 63) ? ~u : (u | 0x8000000000000000ull);  // total order of doubles as unsigned
+}
+__host__ __device__ inline double key_value(unsigned long long u)
+{
+    u = (u >> 63) ? (u & 0x7fffffffffffffffull) : ~u;
+#ifdef __CUDA_ARCH__
+    return __longlong_as_double((long long)u);
+#else
+    double d;
+    memcpy(&d, &u, sizeof d);
+    return d;
+#endif
+}
+
+template <bool FLOW>
+__global__ void __launch_bounds__(256)
+score_filter_kernel(int K, const double *__restrict__ theta, const double *__restrict__ pwz,
+                    long long n, const int32_t *__restrict__ a_doc, const int32_t *__restrict__ b_doc,
+                    const int32_t *__restrict__ a_word, const int32_t *__restrict__ b_word,
+                    double dflt, double tol, long long idx_base, unsigned long long *surv_key,
+                    unsigned long long *surv_idx, unsigned long long cap,
+                    unsigned long long *counter)
+{
+    const bool vec2 = (K % 2) == 0;
+    const int lane = threadIdx.x & 31;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    // whole warps iterate together so the ballot below is over a full warp
+    for (long long base = (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride) {
+        const long long e = base + lane;
+        bool keep = false;
+        double key = 0.0;
+        if (e < n) {
+            const double sa = side_score(theta, pwz, K, a_doc[e], a_word[e], dflt, vec2);
+            if (FLOW) {
+                const double sb = side_score(theta, pwz, K, b_doc[e], b_word[e], dflt, vec2);
+                key = (sb < sa) ? sb : sa;  // flow_post_lda.scala:238
+            } else {
+                key = sa;
+            }
+            keep = key < tol;  // strict, flow_post_lda.scala:245
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (m) {
+            unsigned long long pos = 0;
+            if (lane == __ffs(m) - 1) pos = atomicAdd(counter, (unsigned long long)__popc(m));
+            pos = __shfl_sync(0xffffffffu, pos, __ffs(m) - 1);
+            if (keep) {
+                pos += __popc(m & ((1u << lane) - 1u));
+                if (pos < cap) {
+                    surv_key[pos] = key_bits(key);
+                    surv_idx[pos] = (unsigned long long)(idx_base + e);
+                }
+            }
+        }
+    }
+}
+
+// src/dst score of the ranked survivors (what the Scala stage appends to a row).
+template <bool FLOW>
+__global__ void rescored_kernel(int K, const double *theta, const double *pwz, long long m,
+                                const unsigned long long *idx, long long idx_base,
+                                const int32_t *a_doc, const int32_t *b_doc, const int32_t *a_word,
+                                const int32_t *b_word, double dflt, double *out_a, double *out_b)
+{
+    const bool vec2 = (K % 2) == 0;
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < m;
+         r += (long long)gridDim.x * blockDim.x) {
+        const long long e = (long long)idx[r] - idx_base;
+        out_a[r] = side_score(theta, pwz, K, a_doc[e], a_word[e], dflt, vec2);
+        if (FLOW) out_b[r] = side_score(theta, pwz, K, b_doc[e], b_word[e], dflt, vec2);
+    }
+}
+
+// ------------------------------------------------------------------- radix sort
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ROUNDS = 16;                          // rounds of 32 keys per warp
+constexpr int RS_TILE = RS_THREADS * RS_ROUNDS;        // keys per block
+constexpr int RS_MAX_PASSES = 16;                      // 8 index digits + 8 key digits
+
+__device__ __forceinline__ unsigned digit_of(const unsigned long long *key,
+                                             const unsigned long long *idx, long long i, int pass)
+{
+    // passes 0..7 take the event index (minor), passes 8..15 the key (major)
+    return (pass < 8) ? (unsigned)((idx[i] >> (8 * pass)) & 255u)
+                      : (unsigned)((key[i] >> (8 * (pass - 8))) & 255u);
+}
+
+// totals[pass][digit] over all survivors, every pass at once.
+__global__ void __launch_bounds__(RS_THREADS)
+radix_totals_kernel(const unsigned long long *key, const unsigned long long *idx, long long n,
+                    unsigned long long *totals)
+{
+    __shared__ unsigned int sh[RS_MAX_PASSES][256];
+    for (int i = threadIdx.x; i < RS_MAX_PASSES * 256; i += blockDim.x) (&sh[0][0])[i] = 0;
+    __syncthreads();
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int p = 0; p < RS_MAX_PASSES; p++) atomicAdd(&sh[p][digit_of(key, idx, i, p)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < RS_MAX_PASSES * 256; i += blockDim.x) {
+        const unsigned v = (&sh[0][0])[i];
+        if (v) atomicAdd(&totals[i], (unsigned long long)v);
+    }
+}
+
+// counts[digit][tile] for one pass.
+__global__ void __launch_bounds__(RS_THREADS)
+radix_count_kernel(const unsigned long long *key, const unsigned long long *idx, long long n,
+                   int pass, int ntiles, unsigned long long *counts)
+{
+    __shared__ unsigned int sh[256];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    const long long lo = (long long)blockIdx.x * RS_TILE;
+    const long long hi = min(n, lo + RS_TILE);
+    for (long long i = lo + threadIdx.x; i < hi; i += RS_THREADS)
+        atomicAdd(&sh[digit_of(key, idx, i, pass)], 1u);
+    __syncthreads();
+    counts[(size_t)threadIdx.x * ntiles + blockIdx.x] = sh[threadIdx.x];
+}
+
+// exclusive scan of counts (digit-major, length 256*ntiles), in place, one block.
+__global__ void __launch_bounds__(1024) radix_scan_kernel(unsigned long long *counts, long long len)
+{
+    __shared__ unsigned long long part[1024];
+    const long long per = (len + 1023) / 1024;
+    const long long lo = min(len, (long long)threadIdx.x * per), hi = min(len, lo + per);
+    unsigned long long s = 0;
+    for (long long i = lo; i < hi; i++) s += counts[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long run = 0;
+        for (int i = 0; i < 1024; i++) { const unsigned long long t = part[i]; part[i] = run; run += t; }
+    }
+    __syncthreads();
+    unsigned long long run = part[threadIdx.x];
+    for (long long i = lo; i < hi; i++) { const unsigned long long t = counts[i]; counts[i] = run; run += t; }
+}
+
+// Stable scatter of one pass.  A warp owns RS_ROUNDS*32 consecutive keys and
+// walks them in order; ranks inside a round come from match_any.
+__global__ void __launch_bounds__(RS_THREADS)
+radix_scatter_kernel(const unsigned long long *kin, const unsigned long long *vin,
+                     unsigned long long *kout, unsigned long long *vout, long long n, int pass,
+                     int ntiles, const unsigned long long *offsets)
+{
+    __shared__ unsigned long long base[RS_WARPS][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&base[0][0])[i] = 0;
+    __syncthreads();
+    const long long wlo = (long long)blockIdx.x * RS_TILE + (long long)warp * (RS_ROUNDS * 32);
+    // phase 1: digit counts of this warp's keys
+    for (int r = 0; r < RS_ROUNDS; r++) {
+        const long long i = wlo + r * 32 + lane;
+        const bool ok = i < n;
+        const unsigned d = ok ? digit_of(kin, vin, i, pass) : (0x10000u + lane);
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        if (ok && lane == __ffs(peers) - 1) base[warp][d] += __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    // phase 2: first output slot of every (warp, digit)
+    {
+        const int d = threadIdx.x;  // 256 threads, 256 digits
+        unsigned long long run = offsets[(size_t)d * ntiles + blockIdx.x];
+        for (int w = 0; w < RS_WARPS; w++) {
+            const unsigned long long t = base[w][d];
+            base[w][d] = run;
+            run += t;
+        }
+    }
+    __syncthreads();
+    // phase 3: same walk, now placing
+    for (int r = 0; r < RS_ROUNDS; r++) {
+        const long long i = wlo + r * 32 + lane;
+        const bool ok = i < n;
+        const unsigned d = ok ? digit_of(kin, vin, i, pass) : (0x10000u + lane);
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        unsigned long long pos = 0;
+        if (ok) pos = base[warp][d] + __popc(peers & ((1u << lane) - 1u));
+        __syncwarp();
+        if (ok && lane == __ffs(peers) - 1) base[warp][d] += __popc(peers);
+        __syncwarp();
+        if (ok) {
+            kout[pos] = kin[i];
+            vout[pos] = vin[i];
+        }
+    }
+}
+
+// ---------------------------------------------------------- lda_post.py on device
+// theta = gamma / sum(gamma), python sum(): left to right (lda_post.py:44-54)
+__global__ void theta_kernel(int D, int K, const double *gamma, double *theta)
+{
+    for (int d = blockIdx.x * blockDim.x + threadIdx.x; d < D; d += gridDim.x * blockDim.x) {
+        const double *g = gamma + (size_t)d * K;
+        double total = 0.0;
+        for (int k = 0; k < K; k++) total = __dadd_rn(total, g[k]);
+        for (int k = 0; k < K; k++) theta[(size_t)d * K + k] = (total > 0.0) ? g[k] / total : 0.0;
+    }
+}
+// pwz[w][k] = exp(beta[k][w]) / sum_w exp(beta[k][w]), sum left to right (lda_post.py:88-96).
+// One block per topic; thread 0 forms the sequential total from the staged exps.
+__global__ void pwz_kernel(int K, int V, const double *beta, double *raw, double *pwz)
+{
+    const int k = blockIdx.x;
+    __shared__ double total_sh;
+    for (int w = threadIdx.x; w < V; w += blockDim.x) raw[(size_t)k * V + w] = exp(beta[(size_t)k * V + w]);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double total = 0.0;
+        for (int w = 0; w < V; w++) total = __dadd_rn(total, raw[(size_t)k * V + w]);
+        total_sh = total;
+    }
+    __syncthreads();
+    const double total = total_sh;
+    for (int w = threadIdx.x; w < V; w += blockDim.x) pwz[(size_t)w * K + k] = raw[(size_t)k * V + w] / total;
+}
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    int reserve(size_t need)
+    {
+        if (need <= bytes) return ONI_OK;
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+        ONI_CUDA(cudaMalloc(&p, need ? need : 1));
+        bytes = need;
+        return ONI_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+
+}  // namespace
+
+// ------------------------------------------------------------- scoring context
+struct oni_score_ctx {
+    int device = 0, K = 0, D = 0, V = 0, sm_count = 0;
+    cudaStream_t stream = nullptr;
+    double *d_theta = nullptr, *d_pwz = nullptr;
+    unsigned long long *d_counter = nullptr, *d_totals = nullptr;
+    DevBuf key[2], idx[2], counts, ev[4], out_a, out_b;
+    unsigned long long cap = 0;     // survivor capacity (entries)
+    unsigned long long n_surv = 0;  // survivors of the last run
+    int cur = 0;                    // which ping-pong buffer holds the ranked list
+    int64_t launches = 0;
+    float ms_score = 0, ms_sort = 0;
+    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
+};
+
+extern "C" int oni_score_create(int32_t device, int32_t K, int32_t D, int32_t V, const double *theta,
+                                const double *pwz, oni_score_ctx **out)
+{
+    if (!out || !theta || !pwz || K < 1 || D < 0 || V < 0)
+        return oni_set_error(ONI_ERR_ARG, "score_create: bad argument");
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return oni_set_error(ONI_ERR_CUDA, "no CUDA device: this engine has no CPU path");
+    if (device < 0 || device >= ndev) return oni_set_error(ONI_ERR_ARG, "device %d of %d", device, ndev);
+    ONI_CUDA(cudaSetDevice(device));
+    oni_score_ctx *c = new oni_score_ctx();
+    c->device = device; c->K = K; c->D = D; c->V = V;
+    cudaDeviceProp prop;
+    ONI_CUDA(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    ONI_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    ONI_CUDA(cudaEventCreate(&c->e0)); ONI_CUDA(cudaEventCreate(&c->e1)); ONI_CUDA(cudaEventCreate(&c->e2));
+    ONI_CUDA(cudaMalloc((void **)&c->d_theta, sizeof(double) * std::max<size_t>(1, (size_t)D * K)));
+    ONI_CUDA(cudaMalloc((void **)&c->d_pwz, sizeof(double) * std::max<size_t>(1, (size_t)V * K)));
+    ONI_CUDA(cudaMalloc((void **)&c->d_counter, sizeof(unsigned long long)));
+    ONI_CUDA(cudaMalloc((void **)&c->d_totals, sizeof(unsigned long long) * RS_MAX_PASSES * 256));
+    ONI_CUDA(cudaMemcpy(c->d_theta, theta, sizeof(double) * (size_t)D * K, cudaMemcpyHostToDevice));
+    ONI_CUDA(cudaMemcpy(c->d_pwz, pwz, sizeof(double) * (size_t)V * K, cudaMemcpyHostToDevice));
+    *out = c;
+    return ONI_OK;
+}
+
+extern "C" void oni_score_destroy(oni_score_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaFree(c->d_theta); cudaFree(c->d_pwz); cudaFree(c->d_counter); cudaFree(c->d_totals);
+    for (auto &b : c->key) b.release();
+    for (auto &b : c->idx) b.release();
+    for (auto &b : c->ev) b.release();
+    c->counts.release(); c->out_a.release(); c->out_b.release();
+    if (c->e0) cudaEventDestroy(c->e0);
+    if (c->e1) cudaEventDestroy(c->e1);
+    if (c->e2) cudaEventDestroy(c->e2);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+static int reserve_survivors(oni_score_ctx *c, unsigned long long cap)
+{
+    if (cap <= c->cap) return ONI_OK;
+    // growing keeps what is already there (chunked runs append across calls)
+    for (int b = 0; b < 2; b++) {
+        DevBuf nk, ni;
+        ONI_TRY(nk.reserve(cap * 8)); ONI_TRY(ni.reserve(cap * 8));
+        if (c->cap && b == c->cur) {
+            ONI_CUDA(cudaMemcpyAsync(nk.p, c->key[b].p, c->cap * 8, cudaMemcpyDeviceToDevice, c->stream));
+            ONI_CUDA(cudaMemcpyAsync(ni.p, c->idx[b].p, c->cap * 8, cudaMemcpyDeviceToDevice, c->stream));
+            ONI_CUDA(cudaStreamSynchronize(c->stream));
+        }
+        c->key[b].release(); c->idx[b].release();
+        c->key[b] = nk; c->idx[b] = ni;
+    }
+    c->cap = cap;
+    return ONI_OK;
+}
+
+// Start a scoring run (clears the survivor list).
+extern "C" int oni_score_begin(oni_score_ctx *c)
+{
+    if (!c) return oni_set_error(ONI_ERR_ARG, "score_begin: null context");
+    ONI_CUDA(cudaSetDevice(c->device));
+    ONI_CUDA(cudaMemsetAsync(c->d_counter, 0, sizeof(unsigned long long), c->stream));
+    c->n_surv = 0; c->cur = 0; c->ms_score = c->ms_sort = 0;
+    return ONI_OK;
+}
+
+// Score n events whose indices are on the device; survivors accumulate.
+// idx_base = global index of the chunk's first event.
+extern "C" int oni_score_events_device(oni_score_ctx *c, int32_t is_flow, int64_t n, int64_t idx_base,
+                                       const int32_t *a_doc, const int32_t *b_doc,
+                                       const int32_t *a_word, const int32_t *b_word, double tol)
+{
+    if (!c || n < 0 || (n > 0 && (!a_doc || !a_word || (is_flow && (!b_doc || !b_word)))))
+        return oni_set_error(ONI_ERR_ARG, "score_events: bad argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    if (n == 0) return ONI_OK;
+    const double dflt = is_flow ? 0.05 : 0.1;
+    const int blocks = (int)std::min<long long>((n + 255) / 256, (long long)c->sm_count * 16);
+    if (c->cap == 0) ONI_TRY(reserve_survivors(c, std::max<unsigned long long>(1u << 20, (unsigned long long)n / 64)));
+    for (int attempt = 0; attempt < 2; attempt++) {
+        ONI_CUDA(cudaEventRecord(c->e0, c->stream));
+        if (is_flow)
+            score_filter_kernel<true><<<blocks, 256, 0, c->stream>>>(
+                c->K, c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base,
+                (unsigned long long *)c->key[0].p, (unsigned long long *)c->idx[0].p, c->cap, c->d_counter);
+        else
+            score_filter_kernel<false><<<blocks, 256, 0, c->stream>>>(
+                c->K, c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base,
+                (unsigned long long *)c->key[0].p, (unsigned long long *)c->idx[0].p, c->cap, c->d_counter);
+        c->launches++;
+        ONI_CUDA(cudaEventRecord(c->e1, c->stream));
+        unsigned long long total = 0;
+        ONI_CUDA(cudaMemcpyAsync(&total, c->d_counter, sizeof total, cudaMemcpyDeviceToHost, c->stream));
+        ONI_CUDA(cudaStreamSynchronize(c->stream));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->e0, c->e1);
+        if (total <= c->cap) { c->n_surv = total; c->ms_score += ms; return ONI_OK; }
+        // the list overflowed: grow to what was counted, rewind this chunk, run it again
+        const unsigned long long before = c->n_surv;
+        ONI_TRY(reserve_survivors(c, total + total / 8));
+        ONI_CUDA(cudaMemcpyAsync(c->d_counter, &before, sizeof before, cudaMemcpyHostToDevice, c->stream));
+        ONI_CUDA(cudaStreamSynchronize(c->stream));
+    }
+    return oni_set_error(ONI_ERR_CUDA, "score_events: survivor list overflowed twice");
+}
+
+// Rank the accumulated survivors (ascending key, ties by event index).
+extern "C" int oni_score_rank(oni_score_ctx *c, int64_t *n_survivors)
+{
+    if (!c) return oni_set_error(ONI_ERR_ARG, "score_rank: null context");
+    ONI_CUDA(cudaSetDevice(c->device));
+    const long long n = (long long)c->n_surv;
+    if (n_survivors) *n_survivors = n;
+    c->cur = 0;
+    if (n <= 1) return ONI_OK;
+    cudaStream_t s = c->stream;
+    ONI_CUDA(cudaEventRecord(c->e1, s));
+    ONI_CUDA(cudaMemsetAsync(c->d_totals, 0, sizeof(unsigned long long) * RS_MAX_PASSES * 256, s));
+    const int tblocks = (int)std::min<long long>((n + RS_THREADS - 1) / RS_THREADS, (long long)c->sm_count * 8);
+    radix_totals_kernel<<<tblocks, RS_THREADS, 0, s>>>((unsigned long long *)c->key[0].p,
+                                                        (unsigned long long *)c->idx[0].p, n, c->d_totals);
+    c->launches++;
+    std::vector<unsigned long long> totals((size_t)RS_MAX_PASSES * 256);
+    ONI_CUDA(cudaMemcpyAsync(totals.data(), c->d_totals, sizeof(unsigned long long) * totals.size(),
+                             cudaMemcpyDeviceToHost, s));
+    ONI_CUDA(cudaStreamSynchronize(s));
+    const int ntiles = (int)((n + RS_TILE - 1) / RS_TILE);
+    ONI_TRY(c->counts.reserve(sizeof(unsigned long long) * 256 * (size_t)ntiles));
+    for (int pass = 0; pass < RS_MAX_PASSES; pass++) {
+        bool trivial = false;
+        for (int d = 0; d < 256; d++)
+            if (totals[(size_t)pass * 256 + d] == (unsigned long long)n) { trivial = true; break; }
+        if (trivial) continue;  // every survivor has the same digit here
+        const int in = c->cur, out = c->cur ^ 1;
+        unsigned long long *kin = (unsigned long long *)c->key[in].p, *vin = (unsigned long long *)c->idx[in].p;
+        unsigned long long *kout = (unsigned long long *)c->key[out].p, *vout = (unsigned long long *)c->idx[out].p;
+        unsigned long long *cnt = (unsigned long long *)c->counts.p;
+        radix_count_kernel<<<ntiles, RS_THREADS, 0, s>>>(kin, vin, n, pass, ntiles, cnt);
+        radix_scan_kernel<<<1, 1024, 0, s>>>(cnt, 256LL * ntiles);
+        radix_scatter_kernel<<<ntiles, RS_THREADS, 0, s>>>(kin, vin, kout, vout, n, pass, ntiles, cnt);
+        c->launches += 3;
+        c->cur = out;
+    }
+    ONI_CUDA(cudaEventRecord(c->e2, s));
+    ONI_CUDA(cudaStreamSynchronize(s));
+    ONI_CUDA(cudaGetLastError());
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->e1, c->e2);
+    c->ms_sort = ms;
+    return ONI_OK;
+}
+
+// Copy the first `cap` ranked survivors to the host.
+extern "C" int oni_score_fetch(oni_score_ctx *c, int64_t cap, int64_t *out_idx, double *out_key)
+{
+    if (!c || cap < 0) return oni_set_error(ONI_ERR_ARG, "score_fetch: bad argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    const size_t m = (size_t)std::min<unsigned long long>((unsigned long long)cap, c->n_surv);
+    if (m == 0) return ONI_OK;
+    std::vector<unsigned long long> k(m);
+    if (out_idx)
+        ONI_CUDA(cudaMemcpy(out_idx, c->idx[c->cur].p, sizeof(int64_t) * m, cudaMemcpyDeviceToHost));
+    if (out_key) {
+        ONI_CUDA(cudaMemcpy(k.data(), c->key[c->cur].p, sizeof(unsigned long long) * m, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < m; i++) out_key[i] = key_value(k[i]);
+    }
+    return ONI_OK;
+}
+
+// src/dst scores of the first `cap` ranked survivors; the event index arrays are
+// the device arrays of the chunk that starts at idx_base and holds them all.
+extern "C" int oni_score_fetch_sides(oni_score_ctx *c, int32_t is_flow, int64_t cap, int64_t idx_base,
+                                     const int32_t *a_doc, const int32_t *b_doc, const int32_t *a_word,
+                                     const int32_t *b_word, double *out_a, double *out_b)
+{
+    if (!c || cap < 0) return oni_set_error(ONI_ERR_ARG, "score_fetch_sides: bad argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    const long long m = (long long)std::min<unsigned long long>((unsigned long long)cap, c->n_surv);
+    if (m == 0) return ONI_OK;
+    ONI_TRY(c->out_a.reserve(sizeof(double) * (size_t)m));
+    ONI_TRY(c->out_b.reserve(sizeof(double) * (size_t)m));
+    const double dflt = is_flow ? 0.05 : 0.1;
+    const int blocks = (int)std::min<long long>((m + 255) / 256, 4096);
+    if (is_flow)
+        rescored_kernel<true><<<blocks, 256, 0, c->stream>>>(c->K, c->d_theta, c->d_pwz, m,
+            (unsigned long long *)c->idx[c->cur].p, idx_base, a_doc, b_doc, a_word, b_word, dflt,
+            (double *)c->out_a.p, (double *)c->out_b.p);
+    else
+        rescored_kernel<false><<<blocks, 256, 0, c->stream>>>(c->K, c->d_theta, c->d_pwz, m,
+            (unsigned long long *)c->idx[c->cur].p, idx_base, a_doc, nullptr, a_word, nullptr, dflt,
+            (double *)c->out_a.p, (double *)c->out_b.p);
+    c->launches++;
+    ONI_CUDA(cudaStreamSynchronize(c->stream));
+    ONI_CUDA(cudaGetLastError());
+    if (out_a) ONI_CUDA(cudaMemcpy(out_a, c->out_a.p, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost));
+    if (out_b && is_flow) ONI_CUDA(cudaMemcpy(out_b, c->out_b.p, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost));
+    return ONI_OK;
+}
+
+extern "C" int oni_score_get_stats(oni_score_ctx *c, double *ms_score, double *ms_sort, int64_t *launches)
+{
+    if (!c) return oni_set_error(ONI_ERR_ARG, "score_get_stats: null context");
+    if (ms_score) *ms_score = c->ms_score;
+    if (ms_sort) *ms_sort = c->ms_sort;
+    if (launches) *launches = c->launches;
+    return ONI_OK;
+}
+
+// ------------------------------------------------------ host-buffer entry points
+static int score_host(int32_t device, int is_flow, int32_t K, int32_t D, int32_t V, const double *theta,
+                      const double *pwz, int64_t n, const int32_t *a_doc, const int32_t *b_doc,
+                      const int32_t *a_word, const int32_t *b_word, double tol, int64_t out_cap,
+                      int64_t *out_idx, double *out_key, double *out_a, double *out_b, int64_t *out_n)
+{
+    if (n < 0 || out_cap < 0 || !theta || !pwz) return oni_set_error(ONI_ERR_ARG, "score: bad argument");
+    oni_score_ctx *c = nullptr;
+    ONI_TRY(oni_score_create(device, K, D, V, theta, pwz, &c));
+    int rc = ONI_OK;
+    const int nsrc = is_flow ? 4 : 2;
+    const int32_t *src[4] = {a_doc, a_word, b_doc, b_word};
+    // validate indices on the host: the kernels trust them
+    for (int q = 0; q < nsrc && rc == ONI_OK; q++) {
+        const int32_t lim = (q % 2 == 0) ? D : V;
+        for (int64_t e = 0; e < n; e++)
+            if (src[q][e] >= lim) { rc = oni_set_error(ONI_ERR_ARG, "score: index %d >= %d at event %lld", src[q][e], lim, (long long)e); break; }
+    }
+    // events go up in one piece when they fit (16 B/event flow); chunking keeps
+    // the device footprint bounded for billion-event days
+    const int64_t chunk = std::min<int64_t>(n, (int64_t)1 << 28);
+    if (rc == ONI_OK) rc = oni_score_begin(c);
+    for (int q = 0; q < nsrc && rc == ONI_OK; q++) rc = c->ev[q].reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(chunk, 1));
+    for (int64_t lo = 0; lo < n && rc == ONI_OK; lo += chunk) {
+        const int64_t m = std::min(chunk, n - lo);
+        for (int q = 0; q < nsrc && rc == ONI_OK; q++)
+            if (cudaMemcpyAsync(c->ev[q].p, src[q] + lo, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, c->stream) != cudaSuccess)
+                rc = oni_set_error(ONI_ERR_CUDA, "score: event upload failed");
+        if (rc == ONI_OK)
+            rc = oni_score_events_device(c, is_flow, m, lo, (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p,
+                                         (int32_t *)c->ev[1].p, (int32_t *)c->ev[3].p, tol);
+    }
+    int64_t total = 0;
+    if (rc == ONI_OK) rc = oni_score_rank(c, &total);
+    if (rc == ONI_OK) rc = oni_score_fetch(c, out_cap, out_idx, out_key);
+    if (rc == ONI_OK && (out_a || out_b)) {
+        if (chunk == n) {
+            rc = oni_score_fetch_sides(c, is_flow, out_cap, 0, (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p,
+                                       (int32_t *)c->ev[1].p, (int32_t *)c->ev[3].p, out_a, out_b);
+        } else {
+            rc = oni_set_error(ONI_ERR_ARG, "score: per-side scores need the events in one chunk (n <= 2^28)");
+        }
+    }
+    if (out_n) *out_n = total;
+    oni_score_destroy(c);
+    return rc;
+}
+
+extern "C" int oni_score_flow(int32_t device, int32_t K, int32_t D, int32_t V, const double *theta,
+                              const double *pwz, int64_t n, const int32_t *src_doc, const int32_t *dst_doc,
+                              const int32_t *src_word, const int32_t *dst_word, double tol, int64_t out_cap,
+                              int64_t *out_idx, double *out_key, double *out_src, double *out_dst,
+                              int64_t *out_n)
+{
+    if (n > 0 && (!src_doc || !dst_doc || !src_word || !dst_word))
+        return oni_set_error(ONI_ERR_ARG, "score_flow: null event array");
+    return score_host(device, 1, K, D, V, theta, pwz, n, src_doc, dst_doc, src_word, dst_word, tol, out_cap,
+                      out_idx, out_key, out_src, out_dst, out_n);
+}
+
+extern "C" int oni_score_dns(int32_t device, int32_t K, int32_t D, int32_t V, const double *theta,
+                             const double *pwz, int64_t n, const int32_t *doc, const int32_t *word, double tol,
+                             int64_t out_cap, int64_t *out_idx, double *out_key, int64_t *out_n)
+{
+    if (n > 0 && (!doc || !word)) return oni_set_error(ONI_ERR_ARG, "score_dns: null event array");
+    return score_host(device, 0, K, D, V, theta, pwz, n, doc, nullptr, word, nullptr, tol, out_cap, out_idx,
+                      out_key, nullptr, nullptr, out_n);
+}
+
+// ------------------------------------------------------------------ lda_post.py
+extern "C" int oni_lda_post(int32_t device, int32_t D, int32_t K, int32_t V, const double *gamma,
+                            const double *logbeta, int32_t text_digits, double *theta, double *pwz)
+{
+    if (D < 0 || K < 1 || V < 0 || (text_digits != 0 && (text_digits < 1 || text_digits > 17)))
+        return oni_set_error(ONI_ERR_ARG, "lda_post: bad argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return oni_set_error(ONI_ERR_CUDA, "no CUDA device: this engine has no CPU path");
+    ONI_CUDA(cudaSetDevice(device));
+    char fmt[16];
+    snprintf(fmt, sizeof fmt, "%%.%dg", text_digits);
+    auto roundtrip = [&](double *a, size_t n) {
+        if (!text_digits) return;
+        char buf[64];
+        for (size_t i = 0; i < n; i++) {  // Python-2 str(float): 12 significant digits
+            snprintf(buf, sizeof buf, fmt, a[i]);
+            a[i] = strtod(buf, nullptr);
+        }
+    };
+    if (gamma && theta && D > 0) {
+        DevBuf g, t;
+        ONI_TRY(g.reserve(sizeof(double) * (size_t)D * K)); ONI_TRY(t.reserve(sizeof(double) * (size_t)D * K));
+        ONI_CUDA(cudaMemcpy(g.p, gamma, sizeof(double) * (size_t)D * K, cudaMemcpyHostToDevice));
+        theta_kernel<<<std::min(4096, (D + 127) / 128), 128>>>(D, K, (double *)g.p, (double *)t.p);
+        ONI_CUDA(cudaMemcpy(theta, t.p, sizeof(double) * (size_t)D * K, cudaMemcpyDeviceToHost));
+        g.release(); t.release();
+        roundtrip(theta, (size_t)D * K);
+    }
+    if (logbeta && pwz && V > 0) {
+        DevBuf b, r, p;
+        ONI_TRY(b.reserve(sizeof(double) * (size_t)V * K)); ONI_TRY(r.reserve(sizeof(double) * (size_t)V * K));
+        ONI_TRY(p.reserve(sizeof(double) * (size_t)V * K));
+        ONI_CUDA(cudaMemcpy(b.p, logbeta, sizeof(double) * (size_t)V * K, cudaMemcpyHostToDevice));
+        pwz_kernel<<<K, 256>>>(K, V, (double *)b.p, (double *)r.p, (double *)p.p);
+        ONI_CUDA(cudaMemcpy(pwz, p.p, sizeof(double) * (size_t)V * K, cudaMemcpyDeviceToHost));
+        b.release(); r.release(); p.release();
+        roundtrip(pwz, (size_t)V * K);
+    }
+    ONI_CUDA(cudaGetLastError());
+    return ONI_OK;
+}

@@ -1,0 +1,99 @@
+"""The C-ABI library loads, exports every symbol include/oni_lda.h declares, and
+its host-only entry points (settings / corpus parser / writers) honour the
+reference's file grammar byte for byte.  No GPU needed; no compute calls."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from oni_ml_b200 import _lib, files, lda
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "oni_lda.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(oni_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = C.CDLL(_lib.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 40
+    for n in names:
+        assert hasattr(lib, n), "liboni_lda.so lacks %s" % n
+    # and the binding table covers the header
+    assert set(names) == set(_lib.SIGNATURES), set(names) ^ set(_lib.SIGNATURES)
+    assert _lib.load().oni_version().startswith(b"oni-lda-b200")
+
+
+def test_read_settings_shipped_and_fixed(tmp_path, golden_dir):
+    st = lda.read_settings(os.path.join(golden_dir, "c0_k20", "settings.txt"))
+    assert (st.var_max_iter, st.em_max_iter, st.estimate_alpha) == (20, 20, 1)
+    # thresholds are floats (lda-inference.h:10): 1e-6 -> 9.99999997e-07
+    assert float(st.var_converged) == float(np.float32(1e-6)) != 1e-6
+    st = lda.read_settings(os.path.join(golden_dir, "c0_k5_fixed", "settings.txt"))
+    assert (st.var_max_iter, st.em_max_iter, st.estimate_alpha) == (5, 6, 0)
+    st = lda.read_settings(os.path.join(golden_dir, "c0_k37_unbounded", "settings.txt"))
+    assert st.var_max_iter == -1
+    with pytest.raises(_lib.OniError) as e:
+        lda.read_settings(str(tmp_path / "nope.txt"))
+    assert e.value.code == 2
+
+
+def test_read_corpus_matches_python_reader(golden_dir, c0_corpus):
+    c = lda.read_corpus(os.path.join(golden_dir, "c0_model.dat"))
+    assert c.num_docs == c0_corpus.num_docs == 403
+    assert c.num_terms == c0_corpus.num_terms == 300
+    assert np.array_equal(c.doc_ptr, c0_corpus.doc_ptr)
+    assert np.array_equal(c.word, c0_corpus.word)
+    assert np.array_equal(c.count, c0_corpus.count)
+    # the grammar's edge cases survive: empty document, repeated word id
+    lens = np.diff(c.doc_ptr)
+    assert lens[-3] == 0 and lens[-1] == 3 and list(c.word[-3:]) == [11, 11, 11]
+
+
+def test_read_corpus_rejects_garbage(tmp_path):
+    p = tmp_path / "bad.dat"
+    p.write_text("2 1:1 x:3\n")
+    with pytest.raises(_lib.OniError) as e:
+        lda.read_corpus(str(p))
+    assert e.value.code == 2
+    with pytest.raises(_lib.OniError):
+        lda.read_corpus(str(tmp_path / "missing.dat"))
+
+
+def test_writers_byte_identical_to_reference(tmp_path, golden_dir):
+    g = os.path.join(golden_dir, "c0_k20")
+    beta = files.read_matrix(os.path.join(g, "final.beta"))
+    other = files.read_other(os.path.join(g, "final.other"))
+    gamma = files.read_matrix(os.path.join(g, "final.gamma"))
+    lda.save_model(str(tmp_path / "final"), beta, other["alpha"])
+    lda.save_gamma(str(tmp_path / "final.gamma"), gamma)
+    for name in ("final.beta", "final.other", "final.gamma"):
+        assert open(tmp_path / name).read() == open(os.path.join(g, name)).read(), name
+
+
+def test_compute_fails_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(_lib.OniError) as e:
+        lda.LdaEngine(0, 20, 300, _lib.Settings.shipped())
+    assert e.value.code == 3 and "no CPU path" in str(e.value)
+    th = np.full((2, 20), 0.05)
+    from oni_ml_b200 import scoring
+    with pytest.raises(_lib.OniError) as e:
+        scoring.score_dns(th, th, [0], [0], 1.0)
+    assert e.value.code == 3
+
+
+def test_cli_usage_and_errors(tmp_path):
+    p = lda.run_cli([])
+    assert "usage : lda est" in p.stdout and p.returncode == 0
+    p = lda.run_cli(["est", "2.5", "20", str(tmp_path / "nosettings"), "1", "x", "random", str(tmp_path)],
+                    check_rc=False)
+    assert p.returncode == 2 and "cannot open settings" in p.stderr

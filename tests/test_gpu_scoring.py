@@ -1,0 +1,133 @@
+"""Event scoring + ranking on the GPU against the oracle restatement
+(oracle/score_oracle.c).  Integer and ordering results must be IDENTICAL; the
+scores are compared bit for bit (unfused multiply/add in topic order on both
+sides)."""
+import numpy as np
+import pytest
+
+from oni_ml_b200 import scoring
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+
+
+def tables(D, V, K, seed):
+    rng = np.random.default_rng(seed)
+    theta = rng.dirichlet(np.full(K, 0.3), size=D)
+    pwz = rng.dirichlet(np.full(V, 0.05), size=K).T.copy()
+    return np.ascontiguousarray(theta), np.ascontiguousarray(pwz)
+
+
+def events(n, D, V, seed, miss=0.01):
+    rng = np.random.default_rng(seed)
+    out = []
+    for lim in (D, D, V, V):
+        a = rng.integers(0, lim, size=n).astype(np.int32)
+        a[rng.random(n) < miss] = -1
+        out.append(a)
+    return out  # src_doc, dst_doc, src_word, dst_word
+
+
+def oracle_flow(theta, pwz, sd, dd, sw, dw, tol):
+    L = pyoracle.lib()
+    n, K = sd.shape[0], theta.shape[1]
+    a = np.zeros(n); b = np.zeros(n)
+    L.orc_score_flow(n, K, theta, pwz, sd, dd, sw, dw, a, b)
+    idx = np.zeros(max(n, 1), np.int64); key = np.zeros(max(n, 1))
+    m = L.orc_rank_below(n, a, b.ctypes.data, tol, n, idx, key)
+    return a, b, idx[:m], key[:m]
+
+
+@pytest.mark.parametrize("n,D,V,K,q", [(1000, 50, 40, 20, 0.3), (200000, 5000, 3000, 20, 0.01),
+                                       (50000, 300, 200, 7, 1.0), (4097, 10, 10, 50, 0.5)])
+def test_flow_ranked_list_identical(n, D, V, K, q):
+    theta, pwz = tables(D, V, K, 1)
+    sd, dd, sw, dw = events(n, D, V, 2)
+    a, b, _, _ = oracle_flow(theta, pwz, sd, dd, sw, dw, np.inf)
+    tol = float(np.quantile(np.minimum(a, b), q)) if q < 1.0 else 10.0
+    _, _, want_idx, want_key = oracle_flow(theta, pwz, sd, dd, sw, dw, tol)
+    got = scoring.score_flow(theta, pwz, sd, dd, sw, dw, tol)
+    assert got["n"] == want_idx.shape[0]
+    assert np.array_equal(got["idx"], want_idx)
+    assert np.array_equal(got["key"].view(np.int64), want_key.view(np.int64))
+    assert np.array_equal(got["src"].view(np.int64), a[want_idx].view(np.int64))
+    assert np.array_equal(got["dst"].view(np.int64), b[want_idx].view(np.int64))
+    assert np.all(np.diff(got["key"]) >= 0)
+
+
+def test_ties_rank_by_event_index_and_misses_use_default_vector():
+    K = 20
+    theta = np.full((3, K), 0.05); pwz = np.full((4, K), 0.05)
+    pwz[1] = np.linspace(0.001, 0.02, K)
+    n = 5000
+    sd = np.zeros(n, np.int32); dd = np.full(n, -1, np.int32)
+    sw = np.zeros(n, np.int32); dw = np.full(n, -1, np.int32)
+    sw[::7] = 1
+    got = scoring.score_flow(theta, pwz, sd, dd, sw, dw, 1.0)
+    a, b, want_idx, want_key = oracle_flow(theta, pwz, sd, dd, sw, dw, 1.0)
+    assert got["n"] == n and np.array_equal(got["idx"], want_idx)
+    # all-miss side: 20 * (0.05*0.05) accumulated sequentially
+    acc = 0.0
+    for _ in range(K):
+        acc = acc + 0.05 * 0.05
+    assert np.all(got["dst"] == acc)
+    # ties (identical keys) come back in ascending event order
+    same = got["key"][1:] == got["key"][:-1]
+    assert same.any() and np.all(np.diff(got["idx"])[same] > 0)
+
+
+def test_threshold_is_strict_and_cap_truncates():
+    theta, pwz = tables(20, 30, 20, 5)
+    sd, dd, sw, dw = events(3000, 20, 30, 6, miss=0.0)
+    a, b, idx, key = oracle_flow(theta, pwz, sd, dd, sw, dw, np.inf)
+    tol = float(key[100])  # exactly the 101st smallest key: strict '<' keeps 100 (no ties expected)
+    got = scoring.score_flow(theta, pwz, sd, dd, sw, dw, tol, out_cap=10)
+    assert got["n"] == int(np.sum(np.minimum(a, b) < tol))
+    assert np.array_equal(got["idx"], idx[:10])
+    none = scoring.score_flow(theta, pwz, sd, dd, sw, dw, 1e-20)  # the contract threshold: nothing survives
+    assert none["n"] == 0 and none["idx"].shape == (0,)
+    nothing = scoring.score_flow(theta, pwz, sd[:0], dd[:0], sw[:0], dw[:0], 1.0)
+    assert nothing["n"] == 0
+
+
+def test_dns_ranked_list_identical():
+    theta, pwz = tables(400, 900, 20, 9)
+    rng = np.random.default_rng(10)
+    n = 123457
+    doc = rng.integers(-1, 400, size=n).astype(np.int32)
+    word = rng.integers(-1, 900, size=n).astype(np.int32)
+    L = pyoracle.lib()
+    s = np.zeros(n)
+    L.orc_score_dns(n, 20, theta, pwz, doc, word, s)
+    tol = float(np.quantile(s, 0.05))
+    idx = np.zeros(n, np.int64); key = np.zeros(n)
+    m = L.orc_rank_below(n, s, None, tol, n, idx, key)
+    got = scoring.score_dns(theta, pwz, doc, word, tol)
+    assert got["n"] == m and np.array_equal(got["idx"], idx[:m])
+    assert np.array_equal(got["key"].view(np.int64), key[:m].view(np.int64))
+
+
+def test_bad_event_index_is_rejected():
+    theta, pwz = tables(5, 5, 20, 1)
+    from oni_ml_b200 import _lib
+    with pytest.raises(_lib.OniError):
+        scoring.score_dns(theta, pwz, [7], [0], 1.0)
+
+
+def test_lda_post_tables_match_oracle(golden_dir):
+    """theta / p(w|z) shaping of lda_post.py from the reference's final.* files."""
+    import os
+    from oni_ml_b200 import files
+    g = os.path.join(golden_dir, "c0_k20")
+    gamma = files.read_matrix(os.path.join(g, "final.gamma"))
+    beta = files.read_matrix(os.path.join(g, "final.beta"))
+    L = pyoracle.lib()
+    th = np.zeros_like(gamma); pw = np.zeros((beta.shape[1], beta.shape[0]))
+    L.orc_theta_from_gamma(gamma.shape[0], gamma.shape[1], gamma, th)
+    L.orc_pwz_from_beta(beta.shape[0], beta.shape[1], beta, pw)
+    theta, pwz = scoring.lda_post(gamma, beta, 12)
+    assert np.array_equal(theta, th)
+    # exp() on the device and in glibc may differ in the last bit before the
+    # 12-digit rounding; allow one unit of the 12th digit
+    assert np.max(np.abs(pwz - pw) / pw) < 2e-12
+    assert np.allclose(theta.sum(1), 1.0, atol=1e-10)
