@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py -- EM throughput of the B200 LDA engine on the flow-day workload.
+
+    python bench.py --gpus N --steps K --warmup W            (ours)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+A step is ONE EM iteration (E-step over every document of the shard, the
+deterministic sufficient-statistics reduction, one all-reduce when N > 1, the
+M-step and the alpha Newton) on BASELINE.json's configs[1] ("flow day": 1M
+documents, 50k-word vocabulary, K=20) per GPU; with N GPUs every rank holds its
+own flow-day-sized shard of documents over the shared vocabulary (weak scaling),
+one process per GPU, and the K x V statistics are summed by one ncclAllReduce
+per iteration.  `value` = tokens (sum of counts) of all ranks x K / time of the K
+timed steps (device time, max over ranks), with the corpus resident in HBM.
+`e2e` = the same metric through the public C-ABI path from HOST buffers: corpus
+upload + index build + K EM iterations + gamma/beta readback.
+
+`--impl reference` times the UNMODIFIED oni-lda-c (oracle/_ref/lda_ref, built by
+oracle/ref_build/Makefile with a forked-process MPI shim) on all host cores, on
+a bounded sample of the same workload; the oracle port is used only if that
+binary is absent.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import shutil
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "lda_em_tokens_per_sec"
+UNIT = "tokens/s"
+K_TOPICS = 20
+ALPHA = 2.5
+SEED = 4357
+WORKLOAD = dict(docs_per_gpu=1_000_000, vocab=50_000, mu=3.5, geom_p=0.25)
+SETTINGS_TXT = "var max iter 20\nvar convergence 1e-6\nem max iter %d\nem convergence 1e-6\nalpha estimate\n"
+
+
+def workload_config(n_gpus, extra=None):
+    cfg = {
+        "workload": "flow day (BASELINE configs[1]): %d IP documents and ~%.0fM (doc,word) pairs per GPU, "
+                    "%d-word vocabulary, K=%d, alpha=%.1f, settings.txt as shipped; one step = one EM iteration"
+                    % (WORKLOAD["docs_per_gpu"], 55.0, WORKLOAD["vocab"], K_TOPICS, ALPHA),
+        "docs_per_gpu": WORKLOAD["docs_per_gpu"], "vocab": WORKLOAD["vocab"], "topics": K_TOPICS,
+        "parallelism": "documents sharded over %d GPU(s), one NCCL all-reduce of the K x V statistics per step" % n_gpus,
+        "l2": "phi working set (8*K bytes per pair, ~8 GB) exceeds the 126 MB L2; no flush needed",
+    }
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if not self.proc:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1])); mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for name, val in zip(names, f[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+            os.remove(self.path)
+        except Exception:
+            pass
+        if sm:
+            out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        return out
+
+
+# ------------------------------------------------------------------ reference arm
+def make_sample_model_dat(path, docs, seed=20160123):
+    from oni_ml_b200.corpus import synth_corpus, write_model_dat
+    c = synth_corpus(docs, WORKLOAD["vocab"], k_true=K_TOPICS, mu=WORKLOAD["mu"],
+                     geom_p=WORKLOAD["geom_p"], seed=seed)
+    write_model_dat(path, c)
+    return c
+
+
+def time_reference(model_dat, tokens, nproc, iters_total, warmup, steps, workdir):
+    """Run the reference binary; per-iteration times from the growth of likelihood.dat
+    (flushed after every EM iteration, lda-estimate.c:266-267)."""
+    from oracle import pyoracle
+    st = os.path.join(workdir, "settings.txt")
+    with open(st, "w") as f:
+        f.write(SETTINGS_TXT % (iters_total - 1))  # the loop runs em_max_iter + 1 iterations
+    out = os.path.join(workdir, "out")
+    shutil.rmtree(out, ignore_errors=True)
+    env = dict(os.environ, ONI_LDA_SEED=str(SEED), ONI_MPI_NP=str(nproc))
+    lik = os.path.join(out, "likelihood.dat")
+    p = subprocess.Popen([pyoracle.REF_BIN, "est", str(ALPHA), str(K_TOPICS), st, str(nproc), model_dat,
+                          "random", out], env=env, stdout=subprocess.DEVNULL)
+    stamps = []
+    t_open = None
+    while True:
+        rc = p.poll()
+        now = time.perf_counter()
+        if t_open is None and os.path.exists(lik):
+            t_open = now  # opened right before the EM loop (lda-estimate.c:179)
+        if t_open is not None:
+            try:
+                n = open(lik).read().count("\n")
+            except OSError:
+                n = 0
+            while len(stamps) < n:
+                stamps.append(now)
+        if rc is not None:
+            break
+        time.sleep(0.005)
+    if p.returncode != 0 or len(stamps) < warmup + steps:
+        raise RuntimeError("reference run failed (rc=%s, %d iterations seen)" % (p.returncode, len(stamps)))
+    t0 = t_open if warmup == 0 else stamps[warmup - 1]
+    elapsed = stamps[warmup + steps - 1] - t0
+    return tokens * steps / elapsed, elapsed / steps * 1e3
+
+
+def time_port(corpus, steps):
+    """Fallback when oracle/_ref is absent: the C restatement, one thread."""
+    from oracle import pyoracle
+    st = pyoracle.Settings(20, 1e-6, max(steps - 1, 2), 1e-6, 1)
+    t0 = time.perf_counter()
+    r = pyoracle.run_em(corpus, K_TOPICS, ALPHA, st, SEED)
+    dt = time.perf_counter() - t0
+    return corpus.tokens * r["iters"] / dt, dt / r["iters"] * 1e3
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import pyoracle
+    cores = len(os.sched_getaffinity(0))
+    have_ref = os.path.exists(pyoracle.REF_BIN)
+    nproc = cores if have_ref else 1
+    docs = min(WORKLOAD["docs_per_gpu"], 2500 * nproc)
+    work = tempfile.mkdtemp(prefix="oni_ref_")
+    try:
+        model = os.path.join(work, "model.dat")
+        c = make_sample_model_dat(model, docs)
+        if have_ref:
+            total = max(args.warmup + args.steps, 3)
+            value, ms = time_reference(model, c.tokens, nproc, total, args.warmup, args.steps, work)
+            kind = "reference"
+        else:
+            value, ms = time_port(c, args.steps)
+            kind = "port"
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+    sample = ("%d documents / %d pairs / %d tokens drawn from the flow-day generator, %d rank(s) of the "
+              "unmodified oni-lda-c over a forked-process MPI shim" % (docs, c.nnz, c.tokens, nproc))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.gpus, {"sample": sample}),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": nproc, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def cpu_baseline_leg():
+    """Rank 0, N=1: the reference on ONE host core on a bounded sample (~10-30 s)."""
+    from oracle import pyoracle
+    docs = 4000
+    work = tempfile.mkdtemp(prefix="oni_cpu_")
+    try:
+        model = os.path.join(work, "model.dat")
+        c = make_sample_model_dat(model, docs)
+        if os.path.exists(pyoracle.REF_BIN):
+            value, ms = time_reference(model, c.tokens, 1, 3, 0, 3, work)
+            kind = "reference"
+        else:
+            value, ms = time_port(c, 3)
+            kind = "port"
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+    return {"value": value, "unit": UNIT, "cores": 1, "kind": kind,
+            "sample": "%d documents / %d pairs / %d tokens of the flow-day generator, 3 EM iterations, "
+                      "one rank of the unmodified oni-lda-c" % (docs, c.nnz, c.tokens),
+            "ms_per_step": ms}
+
+
+# ------------------------------------------------------------------------ our arm
+def our_arm(args):
+    import torch
+    import torch.distributed as dist
+    from oni_ml_b200 import _lib, dist as odist, lda
+    from oni_ml_b200.corpus import Corpus, synth_corpus
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+
+    D, V = args.docs or WORKLOAD["docs_per_gpu"], WORKLOAD["vocab"]
+    ptr, word, count = synth_corpus(D, V, k_true=K_TOPICS, mu=WORKLOAD["mu"], geom_p=WORKLOAD["geom_p"],
+                                    seed=20160123 + rank, device=dev, as_torch=True)
+    nnz = int(word.numel())
+    tokens = int(count.sum(dtype=torch.int64))
+    st = _lib.Settings(20, 1e-6, 10_000, 1e-6, 1)  # shipped thresholds; the loop count is ours
+
+    eng = lda.LdaEngine(local, K_TOPICS, V, st)
+    eng.set_corpus_device(ptr, word, count)
+    eng.init_random(SEED, ALPHA)
+    if world > 1:
+        odist.bootstrap_nccl(eng, rank, world)
+    stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=dev)
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        odist.em_iteration(eng)
+    sync_all()
+    launches0 = eng.stats()["kernel_launches"]
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    per_step = []
+    e0.record(stream)
+    for _ in range(args.steps):
+        lik, conv = odist.em_iteration(eng)
+        s = eng.stats()
+        per_step.append((s["ms_estep_kernel"], s["ms_suffstats"], s["ms_mstep"], s["word_visits"], lik))
+    e1.record(stream)
+    sync_all()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = e0.elapsed_time(e1)
+    launches = eng.stats()["kernel_launches"] - launches0
+    t = torch.tensor([ms_total, float(tokens), float(nnz)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms_total, tokens_all, nnz_all = float(tmax[0]), float(tsum[1]), float(tsum[2])
+    else:
+        tokens_all, nnz_all = float(tokens), float(nnz)
+    value = tokens_all * args.steps / (ms_total * 1e-3)
+
+    # ---- e2e: host buffers -> engine -> host results, K EM iterations
+    eng.close()
+    h_ptr, h_word, h_count = (x.cpu().pin_memory() for x in (ptr, word, count))
+    del ptr, word, count
+    torch.cuda.empty_cache()
+    host = Corpus(h_ptr.numpy(), h_word.numpy(), h_count.numpy(), V)
+    sync_all()
+    t0 = time.perf_counter()
+    eng2 = lda.LdaEngine(local, K_TOPICS, V, st)
+    eng2.set_corpus(host)
+    eng2.init_random(SEED, ALPHA)
+    if world > 1:
+        odist.bootstrap_nccl(eng2, rank, world)
+    for _ in range(args.steps):
+        odist.em_iteration(eng2)
+    gam = eng2.gamma()
+    lb = eng2.logbeta()
+    sync_all()
+    e2e_s = time.perf_counter() - t0
+    eng2.close()
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = tokens_all * args.steps / float(te[0])
+    # bytes the engine copies: tok 8/pair + perm 4/pair + doc_ptr/order/total 20/doc (+ chunk lists)
+    h2d = (12 * nnz + 20 * D) / args.steps
+    d2h = (gam.nbytes + lb.nbytes) / args.steps + 48
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    ms_estep = statistics.mean(p[0] for p in per_step)
+    visits = statistics.mean(p[3] for p in per_step)
+    peak, peak_src = peaks()
+    # algorithmic bytes of the E-step kernel per launch: tokens 8/pair read, final phi
+    # 8K/pair written, gamma 8K/doc written, log-beta table 8KV read once
+    alg_bytes = nnz * (8 + 8 * K_TOPICS) + 8 * K_TOPICS * D + 8 * K_TOPICS * V
+    achieved = alg_bytes / (ms_estep * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(world, {"pairs_per_gpu": nnz, "tokens_per_gpu": tokens}),
+        "em_iters_per_sec": args.steps / (ms_total * 1e-3),
+        "pairs_per_sec": nnz_all * args.steps / (ms_total * 1e-3),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "seconds": float(te[0]),
+                "what": "LdaEngine from pinned host CSR: upload + index build + %d EM iterations + gamma/beta readback" % args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "estep_kernel<G=4,T=5>", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": int(alg_bytes), "ms_per_launch": ms_estep,
+                     "note": "fp64-pipe bound, not HBM bound: %.3g (word,topic) visits per launch, each a "
+                             "digamma+exp in fp64" % (visits * K_TOPICS)},
+        "breakdown_ms": {"estep_kernel": ms_estep, "suffstats": statistics.mean(p[1] for p in per_step),
+                         "mstep": statistics.mean(p[2] for p in per_step)},
+        "word_visits_per_step": visits,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            line["cpu_baseline"] = cpu_baseline_leg()
+        except Exception as e:  # the GPU numbers stand on their own
+            line["cpu_baseline"] = {"error": str(e)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--docs", type=int, default=0, help="documents per GPU (default: the flow-day 1M)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    return our_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
