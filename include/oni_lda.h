@@ -262,6 +262,44 @@ int oni_score_fetch_sides(oni_score_ctx *ctx, int32_t is_flow, int64_t cap, int6
 /* CUDA-event times of the last run and kernels launched so far. */
 int oni_score_get_stats(oni_score_ctx *ctx, double *ms_score, double *ms_sort, int64_t *launches);
 
+/* Flow scoring and ranking for callers that must not allocate.
+ * (No counterpart in the reference: an addition of this library.)
+ *
+ * Meant for hosts whose device memory is spoken for before they call us: an
+ * executor that was given a fixed slice of the GPU by a pool allocator, a
+ * serving process that reserved everything at start-up, or one that runs
+ * latency-critical streams beside this call.  For them cudaMalloc/cudaFree can
+ * fail late (the pool holds the memory) and stall the whole device while they
+ * run, so this entry point calls neither, nor any routine that allocates.
+ *
+ * Same result as oni_score_flow (survivors with key < tol, ascending by key,
+ * ties by event index), but
+ *   - every array is DEVICE memory the caller owns, on `device`: theta [D][K],
+ *     pwz [V][K], the four event index arrays [num_events] (index < 0 = lookup
+ *     miss; indices are NOT range-checked here), and the outputs d_out_idx /
+ *     d_out_key [out_cap] (either may be NULL); *out_n (host) receives the
+ *     number of survivors;
+ *   - the working memory is a fixed array inside the library image (about
+ *     8.2 MB, present on every GPU that loads the library until the process
+ *     exits) with room for ONI_NOALLOC_MAX_SURVIVORS events below the
+ *     threshold.  More survivors than that, or out_cap above it, is refused
+ *     with ONI_ERR_ARG and a message; use oni_score_flow then;
+ *   - the first call on a device looks up the array's device address
+ *     (cudaGetSymbolAddress); make that first call before starting any stream
+ *     capture on that device;
+ *   - all calls on a device share the array, which keeps the previous call's
+ *     contents (the call clears what has to start at zero).  Calls that overlap
+ *     on one GPU race with each other: issue them one after the other.
+ * `cuda_stream` is the cudaStream_t to run on (NULL = the default stream); the
+ * call returns after the stream has finished its work. */
+#define ONI_NOALLOC_MAX_SURVIVORS (1 << 18)
+int oni_score_flow_noalloc(int32_t device, int32_t num_topics, const double *d_theta,
+                           const double *d_pwz, int64_t num_events, const int32_t *d_src_doc,
+                           const int32_t *d_dst_doc, const int32_t *d_src_word,
+                           const int32_t *d_dst_word, double tol, int64_t out_cap,
+                           int64_t *d_out_idx, double *d_out_key, int64_t *out_n,
+                           void *cuda_stream);
+
 /* Result shaping of lda_post.py on the device: theta = gamma/sum(gamma)
  * (lda_post.py:44-54) and pwz = exp(beta)/sum_w exp(beta) (lda_post.py:88-96),
  * both passed through 12-significant-digit decimal text when text_digits = 12

@@ -650,3 +650,143 @@ extern "C" int oni_lda_post(int32_t device, int32_t D, int32_t K, int32_t V, con
     ONI_CUDA(cudaGetLastError());
     return ONI_OK;
 }
+
+// ============================================================================
+// Flow scoring + ranking without any allocation.
+//
+// Who this is for: hosts that are not allowed to grow device memory while they
+// run.  A Spark executor or serving process that was handed a fixed slice of
+// the GPU by a pool allocator (everything reserved up front, nothing left for
+// the driver to give out), or a process with latency-critical streams next to
+// this one: cudaMalloc/cudaFree may fail late when the pool owns the memory and
+// they stall every stream of the device while they run.  Such a caller brings
+// its own device buffers for the inputs and outputs; the working memory of the
+// filter and the radix sort lives in the fixed array below instead of in
+// buffers sized and allocated per call.
+//
+// The price is a hard ceiling: the array has room for ONI_NOALLOC_MAX_SURVIVORS
+// events under the threshold (2^18).  It is part of the library image, so every
+// GPU that loads liboni_lda.so carries it (about 8.2 MB) until the process ends.
+//
+// All calls on a device share the array and it keeps whatever the previous call
+// left behind; each call clears the two pieces that must start at zero (the
+// survivor counter and the digit totals) and overwrites the rest before reading
+// it.  Two calls that overlap on the same GPU (different streams or threads)
+// would trample each other's state -- run them one after the other.
+// ============================================================================
+namespace {
+
+constexpr unsigned long long NA_MAX_SURVIVORS = 1ull << 18;
+constexpr unsigned long long NA_MAX_TILES = NA_MAX_SURVIVORS / RS_TILE;  // 64
+// layout, in 8-byte words
+constexpr size_t NA_OFF_KEY0 = 0;
+constexpr size_t NA_OFF_IDX0 = NA_OFF_KEY0 + NA_MAX_SURVIVORS;
+constexpr size_t NA_OFF_KEY1 = NA_OFF_IDX0 + NA_MAX_SURVIVORS;
+constexpr size_t NA_OFF_IDX1 = NA_OFF_KEY1 + NA_MAX_SURVIVORS;
+constexpr size_t NA_OFF_COUNTS = NA_OFF_IDX1 + NA_MAX_SURVIVORS;       // [256][tiles]
+constexpr size_t NA_OFF_TOTALS = NA_OFF_COUNTS + 256 * NA_MAX_TILES;   // [passes][256]
+constexpr size_t NA_OFF_COUNTER = NA_OFF_TOTALS + RS_MAX_PASSES * 256;  // [1] (+ padding)
+constexpr size_t NA_WORDS = NA_OFF_COUNTER + 32;
+
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[NA_WORDS];
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol; the address
+// kernels can use comes from cudaGetSymbolAddress, once per device.
+constexpr int NA_MAX_DEVICES = 64;
+unsigned long long *g_noalloc_addr[NA_MAX_DEVICES] = {};
+
+__global__ void emit_ranked_kernel(const unsigned long long *key, const unsigned long long *idx,
+                                   long long m, long long *out_idx, double *out_key)
+{
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < m;
+         r += (long long)gridDim.x * blockDim.x) {
+        if (out_idx) out_idx[r] = (long long)idx[r];
+        if (out_key) out_key[r] = key_value(key[r]);
+    }
+}
+
+}  // namespace
+
+extern "C" int oni_score_flow_noalloc(int32_t device, int32_t K, const double *d_theta,
+                                      const double *d_pwz, int64_t n, const int32_t *d_src_doc,
+                                      const int32_t *d_dst_doc, const int32_t *d_src_word,
+                                      const int32_t *d_dst_word, double tol, int64_t out_cap,
+                                      int64_t *d_out_idx, double *d_out_key, int64_t *out_n,
+                                      void *cuda_stream)
+{
+    if (K < 1 || n < 0 || out_cap < 0 || !d_theta || !d_pwz || !out_n ||
+        (n > 0 && (!d_src_doc || !d_dst_doc || !d_src_word || !d_dst_word)))
+        return oni_set_error(ONI_ERR_ARG, "score_flow_noalloc: bad argument");
+    if (device < 0 || device >= NA_MAX_DEVICES)
+        return oni_set_error(ONI_ERR_ARG, "score_flow_noalloc: device %d outside 0..%d", device, NA_MAX_DEVICES - 1);
+    if ((unsigned long long)out_cap > NA_MAX_SURVIVORS)
+        return oni_set_error(ONI_ERR_ARG, "score_flow_noalloc: out_cap %lld exceeds the fixed scratch (%llu ranked events)",
+                             (long long)out_cap, NA_MAX_SURVIVORS);
+    ONI_CUDA(cudaSetDevice(device));
+    // set-up, first call on this device: resolve the array's device address
+    if (!g_noalloc_addr[device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return oni_set_error(ONI_ERR_CUDA, "score_flow_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        g_noalloc_addr[device] = (unsigned long long *)p;
+    }
+    unsigned long long *base = g_noalloc_addr[device];
+    unsigned long long *key[2] = {base + NA_OFF_KEY0, base + NA_OFF_KEY1};
+    unsigned long long *idx[2] = {base + NA_OFF_IDX0, base + NA_OFF_IDX1};
+    unsigned long long *counts = base + NA_OFF_COUNTS, *totals = base + NA_OFF_TOTALS;
+    unsigned long long *counter = base + NA_OFF_COUNTER;
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    *out_n = 0;
+
+    // the previous call's leftovers: only these two must start from zero
+    ONI_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned long long), s));
+    ONI_CUDA(cudaMemsetAsync(totals, 0, sizeof(unsigned long long) * RS_MAX_PASSES * 256, s));
+    if (n == 0) { ONI_CUDA(cudaStreamSynchronize(s)); return ONI_OK; }
+
+    int sms = 0;
+    ONI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const int blocks = (int)std::min<long long>((n + 255) / 256, (long long)sms * 16);
+    score_filter_kernel<true><<<blocks, 256, 0, s>>>(K, d_theta, d_pwz, n, d_src_doc, d_dst_doc, d_src_word,
+                                                     d_dst_word, 0.05, tol, 0, key[0], idx[0],
+                                                     NA_MAX_SURVIVORS, counter);
+    unsigned long long total = 0;
+    ONI_CUDA(cudaMemcpyAsync(&total, counter, sizeof total, cudaMemcpyDeviceToHost, s));
+    ONI_CUDA(cudaStreamSynchronize(s));
+    ONI_CUDA(cudaGetLastError());
+    if (total > NA_MAX_SURVIVORS)
+        return oni_set_error(ONI_ERR_ARG,
+                             "score_flow_noalloc: %llu events fall below the threshold, the fixed scratch holds %llu; "
+                             "lower the threshold, split the events, or use oni_score_flow",
+                             total, NA_MAX_SURVIVORS);
+    *out_n = (int64_t)total;
+    const long long m = (long long)total;
+    int cur = 0;
+    if (m > 1) {
+        const int tblocks = (int)std::min<long long>((m + RS_THREADS - 1) / RS_THREADS, (long long)sms * 8);
+        radix_totals_kernel<<<tblocks, RS_THREADS, 0, s>>>(key[0], idx[0], m, totals);
+        unsigned long long h_totals[RS_MAX_PASSES * 256];
+        ONI_CUDA(cudaMemcpyAsync(h_totals, totals, sizeof h_totals, cudaMemcpyDeviceToHost, s));
+        ONI_CUDA(cudaStreamSynchronize(s));
+        const int ntiles = (int)((m + RS_TILE - 1) / RS_TILE);
+        for (int pass = 0; pass < RS_MAX_PASSES; pass++) {
+            bool trivial = false;
+            for (int d = 0; d < 256; d++)
+                if (h_totals[pass * 256 + d] == (unsigned long long)m) { trivial = true; break; }
+            if (trivial) continue;
+            radix_count_kernel<<<ntiles, RS_THREADS, 0, s>>>(key[cur], idx[cur], m, pass, ntiles, counts);
+            radix_scan_kernel<<<1, 1024, 0, s>>>(counts, 256LL * ntiles);
+            radix_scatter_kernel<<<ntiles, RS_THREADS, 0, s>>>(key[cur], idx[cur], key[cur ^ 1], idx[cur ^ 1], m,
+                                                               pass, ntiles, counts);
+            cur ^= 1;
+        }
+    }
+    const long long emit = std::min<long long>(m, out_cap);
+    if (emit > 0 && (d_out_idx || d_out_key)) {
+        const int eblocks = (int)std::min<long long>((emit + 255) / 256, 1024);
+        emit_ranked_kernel<<<eblocks, 256, 0, s>>>(key[cur], idx[cur], emit, (long long *)d_out_idx, d_out_key);
+    }
+    ONI_CUDA(cudaStreamSynchronize(s));
+    ONI_CUDA(cudaGetLastError());
+    return ONI_OK;
+}
