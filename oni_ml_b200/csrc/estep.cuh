@@ -22,7 +22,9 @@
 //     so small that exp(x) could underflow for every topic.
 //   * digamma (utils.c:55-64): same asymptotic series and literal coefficients;
 //     the six recurrence terms 1/(x-1)..1/(x-6) = sum_{j<6} 1/(g+j) are folded
-//     into one rational P(g)/Q(g) (one division instead of six).
+//     into one rational P(g)/Q(g) (one reciprocal instead of seven divisions).
+//   * exp, log and the reciprocal are the branch-free table versions of
+//     devmath.cuh (~1 ulp), so the T topic chains of a lane interleave.
 //   * the bound (lda-inference.c:93-127).  With S_n = sum_k exp(x_k) at visit n
 //     and psi_k^(n) the digamma values used at that visit,
 //         log phi_nk = psi_k^(n) + logbeta_kw - log S_n ,
@@ -40,7 +42,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "devmath.cuh"
+
 namespace oni {
+
+// exp/log tables (3 KB), copied to shared memory by every block of the E-step
+static __device__ const MathTables g_math_tables = ONI_MATH_TABLES_INIT;
 
 // ------------------------------------------------------------ special functions
 // Sum_{j=0..5} 1/(g+j) as P(g)/Q(g); all coefficients positive, so Horner on
@@ -127,6 +134,15 @@ __device__ __forceinline__ double group_max(double v, unsigned gmask)
 template <int G, int T, bool SHIFT>
 __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
 {
+    __shared__ MathTables tabs;
+    {
+        const double *src = reinterpret_cast<const double *>(&g_math_tables);
+        double *dst = reinterpret_cast<double *>(&tabs);
+        for (int i = threadIdx.x; i < (int)(sizeof(MathTables) / sizeof(double)); i += blockDim.x)
+            dst[i] = src[i];
+    }
+    __syncthreads();
+
     const int lane = threadIdx.x & 31;
     const int j = lane & (G - 1);
     const int lead = lane & ~(G - 1);
@@ -136,10 +152,8 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
     const double inv_k = 1.0 / (double)K;
     // lda-inference.c:105-108
     const double lik_const = lgamma(alpha * K) - K * lgamma(alpha);
-
-    bool valid[T];
-#pragma unroll
-    for (int t = 0; t < T; t++) valid[t] = (j + G * t) < K;
+    // T = ceil(K/G): only the last topic slot of a lane can fall outside [0,K)
+    const bool last_ok = (j + G * (T - 1)) < K;
 
     double gam[T], dg[T];
     double acc_a = 0.0, acc_b = 0.0;  // sum c*phi*psi (this lane's topics), sum c*log S
@@ -168,11 +182,12 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
                 s_keep = 1.0; c_keep = 0.0;
                 // lda-inference.c:37-43
                 const double g0 = alpha + p.doc_total[doc] / ((double)K);
-                const double d0 = dev_digamma(g0);
+                const double d0 = digamma_ref(g0, tabs.lg);
 #pragma unroll
                 for (int t = 0; t < T; t++) {
-                    gam[t] = valid[t] ? g0 : 1.0;
-                    dg[t] = valid[t] ? d0 : 0.0;
+                    const bool ok = (t < T - 1) || last_ok;
+                    gam[t] = ok ? g0 : 1.0;
+                    dg[t] = ok ? d0 : 0.0;
                 }
                 have = true;
             }
@@ -190,35 +205,40 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
 #pragma unroll
             for (int t = 0; t < T; t++) {
                 const int k = j + G * t;
-                const double lb = valid[t] ? __ldg(lbrow + k) : 0.0;
-                old[t] = valid[t] ? ((pass == 0) ? inv_k : phrow[k]) : 0.0;
+                const bool ok = (t < T - 1) || last_ok;
+                const double lb = ok ? __ldg(lbrow + k) : 0.0;
+                old[t] = ok ? ((pass == 0) ? inv_k : phrow[k]) : 0.0;
                 x[t] = dg[t] + lb;
             }
             double shift = 0.0;
             if (SHIFT) {
                 double m = -1.0e300;
 #pragma unroll
-                for (int t = 0; t < T; t++) m = valid[t] ? fmax(m, x[t]) : m;
+                for (int t = 0; t < T; t++) m = ((t < T - 1) || last_ok) ? fmax(m, x[t]) : m;
                 shift = group_max<G>(m, gmask);
             }
             double s = 0.0;
 #pragma unroll
             for (int t = 0; t < T; t++) {
-                x[t] = valid[t] ? exp(SHIFT ? (x[t] - shift) : x[t]) : 0.0;
+                const double e = exp_tab(SHIFT ? (x[t] - shift) : x[t], tabs.ex);
+                x[t] = ((t < T - 1) || last_ok) ? e : 0.0;
                 s += x[t];
             }
             s = group_sum<G>(s, gmask);
-            const double rs = 1.0 / s;
+            const double rs = rcp_pos(s);
             double a = 0.0;
 #pragma unroll
             for (int t = 0; t < T; t++) {
-                const int k = j + G * t;
                 const double ph = x[t] * rs;
                 a = fma(ph, dg[t], a);
                 gam[t] = fma(c, ph - old[t], gam[t]);
-                dg[t] = valid[t] ? dev_digamma(gam[t]) : 0.0;
-                if (valid[t]) phrow[k] = ph;
+                x[t] = ph;
             }
+#pragma unroll
+            for (int t = 0; t < T; t++) dg[t] = digamma_ref(gam[t], tabs.lg);
+#pragma unroll
+            for (int t = 0; t < T; t++)
+                if ((t < T - 1) || last_ok) phrow[j + G * t] = x[t];
             acc_a = fma(c, a, acc_a);
             if (SHIFT) acc_s = fma(c, shift, acc_s);  // log S_n = shift + log(sum)
             // log S_n is needed once per visit: lane (n mod G) keeps S_n and the
@@ -227,7 +247,7 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
             if (slot == j) { s_keep = s; c_keep = c; }
             pos++;
             if (slot == G - 1 || pos == end) {
-                acc_b = fma(c_keep, log(s_keep), acc_b);
+                acc_b = fma(c_keep, log_tab(s_keep, tabs.lg), acc_b);
                 s_keep = 1.0; c_keep = 0.0;
             }
         }
@@ -236,8 +256,9 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
             double gs = 0.0, part = 0.0;
 #pragma unroll
             for (int t = 0; t < T; t++) {
-                gs += valid[t] ? gam[t] : 0.0;
-                part += valid[t] ? lgamma(gam[t]) : 0.0;
+                const bool ok = (t < T - 1) || last_ok;
+                gs += ok ? gam[t] : 0.0;
+                part += ok ? lgamma(gam[t]) : 0.0;
             }
             part += acc_b - acc_a;
 #pragma unroll
@@ -266,13 +287,14 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
 #pragma unroll
                 for (int t = 0; t < T; t++) {
                     const int k = j + G * t;
-                    ds += valid[t] ? dg[t] : 0.0;
-                    if (valid[t]) p.gamma[(size_t)doc * K + k] = gam[t];
+                    const bool ok = (t < T - 1) || last_ok;
+                    ds += ok ? dg[t] : 0.0;
+                    if (ok) p.gamma[(size_t)doc * K + k] = gam[t];
                 }
                 ds = group_sum<G>(ds, gmask);
                 if (j == 0) {
                     p.doc_lik[doc] = lik;
-                    p.doc_ass[doc] = ds - K * dev_digamma(gs);
+                    p.doc_ass[doc] = ds - K * digamma_ref(gs, tabs.lg);
                     p.doc_iters[doc] = pass;
                 }
                 have = false;
