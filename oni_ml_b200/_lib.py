@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liboni_lda.so")
+# ONI_LDA_LIB selects another build of the same library (kernel tuning experiments)
+LIB_PATH = os.environ.get("ONI_LDA_LIB") or os.path.join(_HERE, "liboni_lda.so")
 LDA_BIN = os.path.join(_HERE, "bin", "lda")
 
 NCCL_ID_BYTES = 128

@@ -91,10 +91,13 @@ int nccl_load()
 struct oni_lda_ctx {
     int device = 0;
     int K = 0, KP = 0, V = 0, G = 0, T = 0;
+    int T_long = 0;        // long documents run one per warp: G = 32, T_long topics per lane
+    int long_min = 0;      // documents with at least this many pairs are "long" (0 = none)
+    int32_t n_long = 0;    // they are the first n_long entries of `order`
     oni_lda_settings st{};
     int var_max_iter = 0;  // doubles when the bound decreases (lda-estimate.c:261)
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6] = {};
+    cudaStream_t stream = nullptr, stream_long = nullptr;
+    cudaEvent_t ev[6] = {}, ev_fork = nullptr, ev_join = nullptr;
     int sm_count = 0;
 
     // corpus shard
@@ -167,7 +170,7 @@ void free_corpus(oni_lda_ctx *c)
     c->d_perm = nullptr; c->d_items = c->d_items2 = nullptr; c->d_phi = nullptr;
     c->d_gamma = c->d_doc_lik = c->d_doc_ass = nullptr; c->d_doc_iters = nullptr;
     c->d_partial = nullptr;
-    c->D = 0; c->nnz = 0;
+    c->D = 0; c->nnz = 0; c->n_long = 0;
 }
 
 // Host-side, once per corpus: schedule order, word-sorted pair index, chunk lists.
@@ -197,6 +200,9 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *ptr, co
     std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
         return (ptr[a + 1] - ptr[a]) > (ptr[b + 1] - ptr[b]);
     });
+    int32_t n_long = 0;
+    if (c->long_min > 0)
+        while (n_long < D && (ptr[order[n_long] + 1] - ptr[order[n_long]]) >= c->long_min) n_long++;
 
     // counting sort of pair ids by word (stable: document order inside a word)
     std::vector<int64_t> wptr((size_t)V + 1, 0);
@@ -225,7 +231,7 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *ptr, co
     }
 
     free_corpus(c);
-    c->D = D; c->nnz = nnz;
+    c->D = D; c->nnz = nnz; c->n_long = n_long;
     c->n_items = (int32_t)items.size(); c->n_items2 = (int32_t)items2.size(); c->n_partial = n_partial;
     ONI_TRY(dev_alloc(&c->d_tok, (size_t)nnz));
     ONI_TRY(dev_alloc(&c->d_doc_ptr, (size_t)D + 1));
@@ -318,12 +324,22 @@ extern "C" int oni_lda_create(int32_t device, int32_t K, int32_t V, const oni_ld
     ONI_CUDA(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
     ONI_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    ONI_CUDA(cudaStreamCreateWithFlags(&c->stream_long, cudaStreamNonBlocking));
     for (auto &e : c->ev) ONI_CUDA(cudaEventCreate(&e));
+    ONI_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    ONI_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+    // A document's words are visited strictly in order, so a very long document is a
+    // serial chain; those get a whole warp (G = 32) to shorten the chain per visit.
+    if (G < 32) {
+        const char *env = getenv("ONI_LDA_LONG_DOC");
+        c->long_min = env ? atoi(env) : 1024;
+        c->T_long = (K + 31) / 32;
+    }
     ONI_TRY(dev_alloc(&c->d_logbeta_t, (size_t)V * c->KP));
     ONI_TRY(dev_alloc(&c->d_alpha, 1));
     ONI_TRY(dev_alloc(&c->d_ss, c->ss_count()));
     ONI_TRY(dev_alloc(&c->d_block_partial, (size_t)DOC_RED_BLOCKS * 3));
-    ONI_TRY(dev_alloc(&c->d_ticket, 1));
+    ONI_TRY(dev_alloc(&c->d_ticket, 2));
     ONI_TRY(dev_alloc(&c->d_done, 1));
     ONI_TRY(dev_alloc(&c->d_nan, 1));
     ONI_CUDA(cudaMemset(c->d_done, 0, sizeof(unsigned)));
@@ -344,6 +360,9 @@ extern "C" void oni_lda_destroy(oni_lda_ctx *c)
     cudaFree(c->d_ticket); cudaFree(c->d_done); cudaFree(c->d_nan);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto &e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    if (c->stream_long) cudaStreamDestroy(c->stream_long);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -447,14 +466,32 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
     // is hugely negative, i.e. alpha tiny; then use the max-shifted kernel.
     const bool shift = !(c->alpha > 0.01);
 
-    ONI_CUDA(cudaMemsetAsync(c->d_ticket, 0, sizeof(unsigned), s));
+    ONI_CUDA(cudaMemsetAsync(c->d_ticket, 0, 2 * sizeof(unsigned), s));
     ONI_CUDA(cudaEventRecord(c->ev[0], s));
-    if (c->D > 0) {
-        cudaError_t e = launch_estep(c->G, c->T, shift, p, c->sm_count, s);
+    if (c->n_long > 0) {
+        // long documents first, one per warp, on a second stream so that the rest of
+        // the corpus fills the SMs as these drain
+        ONI_CUDA(cudaEventRecord(c->ev_fork, s));
+        ONI_CUDA(cudaStreamWaitEvent(c->stream_long, c->ev_fork, 0));
+        EstepParams pl = p;
+        pl.D = c->n_long;
+        pl.ticket = c->d_ticket + 1;
+        cudaError_t e = launch_estep(32, c->T_long, shift, pl, c->sm_count, c->stream_long);
+        if (e != cudaSuccess)
+            return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=32,T=%d): %s", c->T_long, cudaGetErrorString(e));
+        c->launches++;
+        ONI_CUDA(cudaEventRecord(c->ev_join, c->stream_long));
+    }
+    if (c->D > c->n_long) {
+        EstepParams ps = p;
+        ps.order = c->d_order + c->n_long;
+        ps.D = c->D - c->n_long;
+        cudaError_t e = launch_estep(c->G, c->T, shift, ps, c->sm_count, s);
         if (e != cudaSuccess)
             return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=%d,T=%d): %s", c->G, c->T, cudaGetErrorString(e));
         c->launches++;
     }
+    if (c->n_long > 0) ONI_CUDA(cudaStreamWaitEvent(s, c->ev_join, 0));
     ONI_CUDA(cudaEventRecord(c->ev[1], s));
     ONI_TRY(dispatch_ss(c));
     {

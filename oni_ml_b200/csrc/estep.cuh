@@ -115,6 +115,11 @@ struct EstepParams {
     double var_converged;
 };
 
+__device__ __forceinline__ void prefetch_l1(const void *p)
+{
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
+
 template <int G>
 __device__ __forceinline__ double group_sum(double v, unsigned gmask)
 {
@@ -131,8 +136,13 @@ __device__ __forceinline__ double group_max(double v, unsigned gmask)
 }
 
 // ---------------------------------------------------------------- the kernel
+// Resident blocks per SM the register allocation is tuned for (128-thread blocks).
+#ifndef ONI_ESTEP_MINB
+#define ONI_ESTEP_MINB 3
+#endif
+
 template <int G, int T, bool SHIFT>
-__global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
+__global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepParams p)
 {
     __shared__ MathTables tabs;
     {
@@ -156,12 +166,15 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
     const bool last_ok = (j + G * (T - 1)) < K;
 
     double gam[T], dg[T];
+    double lbc[T], oldc[T];           // rows of the visit at `pos`, loaded one visit ahead
     double acc_a = 0.0, acc_b = 0.0;  // sum c*phi*psi (this lane's topics), sum c*log S
     double acc_s = 0.0;               // SHIFT only: sum c*shift (same in every lane)
     double s_keep = 1.0, c_keep = 0.0;
     double lik_old = 0.0;
     int64_t beg = 0, end = 0, pos = 0;
     int32_t doc = -1, pass = 0;
+    int2 tk = make_int2(0, 0);   // (word, count) of the pair at `pos`
+    int2 tk1 = make_int2(0, 0);  // ... and of the visit after it
     bool have = false, exhausted = false;
 
     while (true) {
@@ -189,6 +202,18 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
                     gam[t] = ok ? g0 : 1.0;
                     dg[t] = ok ? d0 : 0.0;
                 }
+                if (beg < end) {
+                    // prime the one-visit-ahead pipeline (first sweep: old phi = 1/K)
+                    tk = __ldg(p.tok + beg);
+                    tk1 = __ldg(p.tok + ((beg + 1 < end) ? beg + 1 : beg));
+                    const double *lbrow = p.logbeta_t + (size_t)tk.x * KP;
+#pragma unroll
+                    for (int t = 0; t < T; t++) {
+                        const bool ok = (t < T - 1) || last_ok;
+                        lbc[t] = ok ? __ldg(lbrow + j + G * t) : 0.0;
+                        oldc[t] = ok ? inv_k : 0.0;
+                    }
+                }
                 have = true;
             }
         }
@@ -197,18 +222,35 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
 
         if (pos < end) {
             // ---- one word visit (lda-inference.c:50-75)
-            const int2 tk = __ldg(p.tok + pos);
             const double c = (double)tk.y;
-            const double *lbrow = p.logbeta_t + (size_t)tk.x * KP;
             double *phrow = p.phi + (size_t)pos * KP;
-            double x[T], old[T];
+            // Software pipeline: the rows of the NEXT visit (wrapping to the first word
+            // for the next sweep) are requested now and consumed one visit later, so
+            // their latency hides behind this visit's arithmetic.
+            const int64_t npos = (pos + 1 < end) ? pos + 1 : beg;
+            const int64_t n2pos = (npos + 1 < end) ? npos + 1 : beg;
+            const int2 tk2 = __ldg(p.tok + n2pos);
+            const bool next_first_sweep = (pass == 0) && (npos != beg);
+            double lbn[T], oldn[T];
+            {
+                const double *nlb = p.logbeta_t + (size_t)tk1.x * KP;
+                const double *nph = p.phi + (size_t)npos * KP;
+#pragma unroll
+                for (int t = 0; t < T; t++) {
+                    const int k = j + G * t;
+                    const bool ok = (t < T - 1) || last_ok;
+                    lbn[t] = ok ? __ldg(nlb + k) : 0.0;
+                    // (a one-word document rereads the row this visit is about to write;
+                    //  that case is patched below)
+                    oldn[t] = ok ? (next_first_sweep ? inv_k : nph[k]) : 0.0;
+                }
+            }
+            double x[T];
 #pragma unroll
             for (int t = 0; t < T; t++) {
-                const int k = j + G * t;
-                const bool ok = (t < T - 1) || last_ok;
-                const double lb = ok ? __ldg(lbrow + k) : 0.0;
-                old[t] = ok ? ((pass == 0) ? inv_k : phrow[k]) : 0.0;
-                x[t] = dg[t] + lb;
+                x[t] = dg[t] + lbc[t];
+                // gamma + c*(phi - old) (lda-inference.c:69-70), the old part first
+                gam[t] = fma(-c, oldc[t], gam[t]);
             }
             double shift = 0.0;
             if (SHIFT) {
@@ -231,7 +273,7 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
             for (int t = 0; t < T; t++) {
                 const double ph = x[t] * rs;
                 a = fma(ph, dg[t], a);
-                gam[t] = fma(c, ph - old[t], gam[t]);
+                gam[t] = fma(c, ph, gam[t]);
                 x[t] = ph;
             }
 #pragma unroll
@@ -239,6 +281,15 @@ __global__ void __launch_bounds__(128) estep_kernel(const EstepParams p)
 #pragma unroll
             for (int t = 0; t < T; t++)
                 if ((t < T - 1) || last_ok) phrow[j + G * t] = x[t];
+            // rotate the pipeline
+            const bool same_row = (npos == pos);  // one-word document
+#pragma unroll
+            for (int t = 0; t < T; t++) {
+                lbc[t] = lbn[t];
+                oldc[t] = same_row ? x[t] : oldn[t];
+            }
+            tk = tk1;
+            tk1 = tk2;
             acc_a = fma(c, a, acc_a);
             if (SHIFT) acc_s = fma(c, shift, acc_s);  // log S_n = shift + log(sum)
             // log S_n is needed once per visit: lane (n mod G) keeps S_n and the
