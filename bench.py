@@ -209,7 +209,7 @@ def reference_arm(args):
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": nproc, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -236,7 +236,35 @@ def cpu_baseline_leg():
 
 
 # ------------------------------------------------------------------------ our arm
+class QuietStdout:
+    """Libraries (NCCL, torchrun banners) may write to fd 1; the contract is ONE JSON
+    line on stdout, so fd 1 points at stderr until the line is printed."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
+def emit(line):
+    print(json.dumps(line), flush=True)
+
+
 def our_arm(args):
+    with QuietStdout():
+        line = _our_arm(args)
+    if line is not None:
+        emit(line)
+    return 0
+
+
+def _our_arm(args):
     import torch
     import torch.distributed as dist
     from oni_ml_b200 import _lib, dist as odist, lda
@@ -309,30 +337,36 @@ def our_arm(args):
     host = Corpus(h_ptr.numpy(), h_word.numpy(), h_count.numpy(), V)
     sync_all()
     t0 = time.perf_counter()
-    eng2 = lda.LdaEngine(local, K_TOPICS, V, st)
-    eng2.set_corpus(host)
-    eng2.init_random(SEED, ALPHA)
+    marks = [("start", t0)]
+    eng2 = lda.LdaEngine(local, K_TOPICS, V, st); marks.append(("create", time.perf_counter()))
+    eng2.set_corpus(host); marks.append(("set_corpus", time.perf_counter()))
+    eng2.init_random(SEED, ALPHA); marks.append(("init_random", time.perf_counter()))
     if world > 1:
         odist.bootstrap_nccl(eng2, rank, world)
     for _ in range(args.steps):
         odist.em_iteration(eng2)
-    gam = eng2.gamma()
-    lb = eng2.logbeta()
+    marks.append(("em", time.perf_counter()))
+    gam = eng2.gamma(); marks.append(("gamma", time.perf_counter()))
+    lb = eng2.logbeta(); marks.append(("logbeta", time.perf_counter()))
     sync_all()
     e2e_s = time.perf_counter() - t0
+    if rank == 0:
+        print("e2e stages (ms): " + ", ".join("%s %.0f" % (n, (t - p) * 1e3) for (n, t), (_, p)
+                                              in zip(marks[1:], marks[:-1])), file=sys.stderr)
     eng2.close()
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = tokens_all * args.steps / float(te[0])
-    # bytes the engine copies: tok 8/pair + perm 4/pair + doc_ptr/order/total 20/doc (+ chunk lists)
-    h2d = (12 * nnz + 20 * D) / args.steps
+    # bytes the engine uploads: word + count (4 + 4 per pair), doc_ptr (8 per document); the
+    # chunk lists of the reduction are a few MB more
+    h2d = (8 * nnz + 8 * (D + 1)) / args.steps
     d2h = (gam.nbytes + lb.nbytes) / args.steps + 48
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
-        return 0
+        return None
     ms_estep = statistics.mean(p[0] for p in per_step)
     visits = statistics.mean(p[3] for p in per_step)
     peak, peak_src = peaks()
@@ -366,10 +400,105 @@ def our_arm(args):
             line["cpu_baseline"] = cpu_baseline_leg()
         except Exception as e:  # the GPU numbers stand on their own
             line["cpu_baseline"] = {"error": str(e)}
-    print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    return line
+
+
+# ------------------------------------------------------------- scoring workload
+def score_arm(args):
+    with QuietStdout():
+        line = _score_arm(args)
+    emit(line)
     return 0
+
+
+def _score_arm(args):
+    """BASELINE configs[4]: flow events scored from theta [1M x 20] / p(w|z) [50k x 20],
+    threshold filter, ranked ascending.  One step = one pass over all events."""
+    import torch
+    from oni_ml_b200 import scoring
+    from oracle import pyoracle
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    D, V, K, n = WORKLOAD["docs_per_gpu"], WORKLOAD["vocab"], K_TOPICS, args.events
+    g = torch.Generator(device=dev); g.manual_seed(20160127)
+    th = torch._standard_gamma(torch.full((D, K), 0.3, dtype=torch.float64, device=dev), generator=g) + 1e-300
+    th /= th.sum(1, keepdim=True)
+    pw = torch._standard_gamma(torch.full((K, V), 0.05, dtype=torch.float64, device=dev), generator=g) + 1e-300
+    pw = (pw / pw.sum(1, keepdim=True)).T.contiguous()
+    theta, pwz = th.cpu().numpy(), pw.cpu().numpy()
+    del th, pw
+
+    def draw(lim, skew):
+        u = torch.rand(n, generator=g, device=dev)
+        if skew:
+            u = u ** 3  # a few hot words, as a Zipf-like vocabulary gives
+        a = (u * lim).to(torch.int32).clamp_(0, lim - 1)
+        a[torch.rand(n, generator=g, device=dev) < 1e-3] = -1  # lookup misses
+        return a
+    ev = [draw(D, False), draw(D, False), draw(V, True), draw(V, True)]
+    ctx = scoring.ScoreContext(theta, pwz, 0)
+    # threshold at the 1e-3 quantile of a 2M-event sample (so the sort has ~n/1000 keys)
+    m = min(n, 2_000_000)
+    ctx.begin(); ctx.score_flow(*(a[:m] for a in ev), float("inf")); k = ctx.rank()
+    _, keys = ctx.fetch(k)
+    tol = float(keys[max(1, int(1e-3 * m))])
+    for _ in range(args.warmup):
+        ctx.begin(); ctx.score_flow(*ev, tol); ctx.rank()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0); sampler.start()
+    l0 = ctx.stats()["kernel_launches"]
+    ms_score, ms_sort, t0 = [], [], time.perf_counter()
+    for _ in range(args.steps):
+        ctx.begin(); ctx.score_flow(*ev, tol); surv = ctx.rank()
+        st = ctx.stats(); ms_score.append(st["ms_score"]); ms_sort.append(st["ms_sort"])
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    launches = ctx.stats()["kernel_launches"] - l0
+    dev_ms = statistics.mean(ms_score) + statistics.mean(ms_sort)
+    idx, key = ctx.fetch(min(surv, 1_000_000))
+    # e2e: host arrays through oni_score_flow (upload of 16 B/event inside)
+    hev = [a.cpu().pin_memory().numpy() for a in ev]
+    t0 = time.perf_counter()
+    r = scoring.score_flow(theta, pwz, *hev, tol, out_cap=1_000_000, sides=False)
+    e2e_s = time.perf_counter() - t0
+    assert r["n"] == surv and np.array_equal(r["idx"], idx)
+    # parity on a prefix against the oracle, and the CPU baseline from the same call
+    mp = min(n, 10_000_000)
+    L = pyoracle.lib()
+    a = np.zeros(mp); b = np.zeros(mp)
+    t0 = time.perf_counter()
+    L.orc_score_flow(mp, K, theta, pwz, *(h[:mp] for h in hev), a, b)
+    oi = np.zeros(mp, np.int64); ok = np.zeros(mp)
+    mm = L.orc_rank_below(mp, a, b.ctypes.data, tol, mp, oi, ok)
+    cpu_s = time.perf_counter() - t0
+    pre = scoring.score_flow(theta, pwz, *(h[:mp] for h in hev), tol, sides=False)
+    identical = bool(pre["n"] == mm and np.array_equal(pre["idx"], oi[:mm])
+                     and np.array_equal(pre["key"].view(np.int64), ok[:mm].view(np.int64)))
+    peak, peak_src = peaks()
+    achieved = n * (16 + 16 * K + 8) / (statistics.mean(ms_score) * 1e-3) / 1e9
+    return {
+        "metric": "flow_events_scored_per_sec", "value": n / (dev_ms * 1e-3), "unit": "events/s", "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "post-LDA flow scoring (BASELINE configs[4] shape): %d events, theta %dx%d, p(w|z) %dx%d, "
+                               "threshold at the 1e-3 score quantile (%d survivors ranked); one step = all events"
+                               % (n, D, K, V, K, surv), "events": n, "threshold": tol,
+                   "l2": "event indices (16 B/event) and the 160 MB theta table exceed the L2"},
+        "e2e": {"value": n / e2e_s, "unit": "events/s", "h2d_bytes_per_step": 16 * n + theta.nbytes + pwz.nbytes,
+                "d2h_bytes_per_step": 16 * min(surv, 1_000_000), "seconds": e2e_s,
+                "what": "oni_score_flow over host arrays (tables + event indices uploaded inside)"},
+        "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / args.steps * 1e3,
+        "roofline": {"bound": "hbm", "kernel": "score_filter_kernel<flow>", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": n * (16 + 16 * K + 8), "ms_per_launch": statistics.mean(ms_score)},
+        "breakdown_ms": {"score_filter": statistics.mean(ms_score), "rank": statistics.mean(ms_sort)},
+        "ranked_list_identical_to_oracle_on_prefix": identical, "prefix_events": mp,
+        "cpu_baseline": {"value": mp / cpu_s, "unit": "events/s", "cores": 1, "kind": "port",
+                         "sample": "%d-event prefix, oracle/score_oracle.c (no JVM/Spark on this box)" % mp},
+    }
 
 
 def main():
@@ -380,9 +509,14 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--docs", type=int, default=0, help="documents per GPU (default: the flow-day 1M)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="em", choices=["em", "score"],
+                    help="em (default, the headline metric) or score (BASELINE configs[4])")
+    ap.add_argument("--events", type=int, default=250_000_000, help="events for --workload score")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
+    if args.workload == "score":
+        return score_arm(args)
     return our_arm(args)
 
 

@@ -27,8 +27,10 @@
 #include <vector>
 
 #include "common.h"
+#include "corpus_index.cuh"
 #include "estep_launch.h"
 #include "mt19937.h"
+#include "radix_sort.cuh"
 #include "suffstats.cuh"
 
 using namespace oni;
@@ -173,47 +175,106 @@ void free_corpus(oni_lda_ctx *c)
     c->D = 0; c->nnz = 0; c->n_long = 0;
 }
 
-// Host-side, once per corpus: schedule order, word-sorted pair index, chunk lists.
-int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *ptr, const int32_t *word,
-                  const int32_t *count)
+double now_seconds();
+
+struct StageTimer {
+    bool on = getenv("ONI_LDA_TIMING") != nullptr;
+    double t = now_seconds();
+    void lap(const char *what)
+    {
+        if (!on) return;
+        const double n = now_seconds();
+        fprintf(stderr, "[oni timing] %-28s %8.1f ms\n", what, (n - t) * 1e3);
+        t = n;
+    }
+};
+
+// Once per corpus: everything is derived on the device from the CSR arrays
+// (corpus_index.cuh); only the chunk lists of the reduction (one entry per word
+// plus one per 256 pairs) are formed on the host from the word histogram.
+// d_ptr/d_word/d_count: device arrays; h_ptr: host copy of doc_ptr.
+int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, const int64_t *d_ptr,
+                  const int32_t *d_word, const int32_t *d_count)
 {
+    StageTimer tm;
     if (nnz > 0x7fffffffLL)
         return oni_set_error(ONI_ERR_ARG, "shard has %lld pairs; at most 2^31-1 per GPU", (long long)nnz);
     const int V = c->V;
-    for (int64_t i = 0; i < nnz; i++)
-        if (word[i] < 0 || word[i] >= V)
-            return oni_set_error(ONI_ERR_ARG, "word id %d outside [0,%d)", word[i], V);
     for (int32_t d = 0; d < D; d++)
-        if (ptr[d + 1] < ptr[d]) return oni_set_error(ONI_ERR_ARG, "doc_ptr not monotone at %d", d);
-    if (ptr[0] != 0 || ptr[D] != nnz) return oni_set_error(ONI_ERR_ARG, "doc_ptr does not span the pairs");
-
-    std::vector<int2> tok((size_t)nnz);
-    for (int64_t i = 0; i < nnz; i++) tok[i] = make_int2(word[i], count[i]);
-    std::vector<double> total((size_t)D);
-    std::vector<int32_t> order((size_t)D);
-    for (int32_t d = 0; d < D; d++) {
-        int32_t t = 0;  // the reference sums counts in an int (lda.h:27, lda-data.c:47)
-        for (int64_t i = ptr[d]; i < ptr[d + 1]; i++) t += count[i];
-        total[d] = (double)t;
-        order[d] = d;
-    }
-    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
-        return (ptr[a + 1] - ptr[a]) > (ptr[b + 1] - ptr[b]);
-    });
+        if (h_ptr[d + 1] < h_ptr[d]) return oni_set_error(ONI_ERR_ARG, "doc_ptr not monotone at %d", d);
+    if (h_ptr[0] != 0 || h_ptr[D] != nnz) return oni_set_error(ONI_ERR_ARG, "doc_ptr does not span the pairs");
     int32_t n_long = 0;
     if (c->long_min > 0)
-        while (n_long < D && (ptr[order[n_long] + 1] - ptr[order[n_long]]) >= c->long_min) n_long++;
+        for (int32_t d = 0; d < D; d++) n_long += (h_ptr[d + 1] - h_ptr[d]) >= c->long_min;
+    tm.lap("validate doc_ptr");
 
-    // counting sort of pair ids by word (stable: document order inside a word)
-    std::vector<int64_t> wptr((size_t)V + 1, 0);
-    for (int64_t i = 0; i < nnz; i++) wptr[word[i] + 1]++;
-    for (int w = 0; w < V; w++) wptr[w + 1] += wptr[w];
-    std::vector<int32_t> perm((size_t)nnz);
-    {
-        std::vector<int64_t> cur(wptr.begin(), wptr.end() - 1);
-        for (int64_t i = 0; i < nnz; i++) perm[cur[word[i]]++] = (int32_t)i;
+    free_corpus(c);
+    c->D = D; c->nnz = nnz; c->n_long = n_long;
+    cudaStream_t s = c->stream;
+    ONI_TRY(dev_alloc(&c->d_tok, (size_t)nnz));
+    ONI_TRY(dev_alloc(&c->d_doc_ptr, (size_t)D + 1));
+    ONI_TRY(dev_alloc(&c->d_order, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_doc_total, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_perm, (size_t)nnz));
+    ONI_TRY(dev_alloc(&c->d_phi, (size_t)nnz * c->KP));
+    ONI_TRY(dev_alloc(&c->d_gamma, (size_t)D * c->K));
+    ONI_TRY(dev_alloc(&c->d_doc_lik, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_doc_ass, (size_t)D));
+    ONI_TRY(dev_alloc(&c->d_doc_iters, (size_t)D));
+    // scratch of the two sorts (freed below)
+    const size_t m = (size_t)std::max<int64_t>(nnz, D);
+    const size_t ntiles = (m + RS_TILE - 1) / RS_TILE;
+    unsigned long long *key[2] = {nullptr, nullptr}, *idx[2] = {nullptr, nullptr}, *counts = nullptr, *totals = nullptr;
+    int64_t *d_wptr = nullptr;
+    int rc = ONI_OK;
+    auto release = [&]() {
+        cudaFree(key[0]); cudaFree(key[1]); cudaFree(idx[0]); cudaFree(idx[1]);
+        cudaFree(counts); cudaFree(totals); cudaFree(d_wptr);
+    };
+#define ONI_IDX(call) do { rc = (call); if (rc != ONI_OK) { release(); return rc; } } while (0)
+#define ONI_IDX_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { release(); \
+        return oni_set_error(ONI_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } } while (0)
+    for (int b = 0; b < 2; b++) { ONI_IDX(dev_alloc(&key[b], m)); ONI_IDX(dev_alloc(&idx[b], m)); }
+    ONI_IDX(dev_alloc(&counts, 256 * ntiles));
+    ONI_IDX(dev_alloc(&totals, (size_t)RS_MAX_PASSES * 256));
+    ONI_IDX(dev_alloc(&d_wptr, (size_t)V + 1));
+    tm.lap("device allocations");
+
+    const int grid = c->sm_count * 8;
+    ONI_IDX_CUDA(cudaMemcpyAsync(c->d_doc_ptr, d_ptr, sizeof(int64_t) * ((size_t)D + 1), cudaMemcpyDeviceToDevice, s));
+    ONI_IDX_CUDA(cudaMemsetAsync(c->d_nan, 0, sizeof(int32_t), s));
+    // documents: totals + longest-first order (stable: ties keep document order)
+    int cur = 0;
+    if (D > 0) {
+        doc_meta_kernel<<<grid, 256, 0, s>>>(d_ptr, d_count, D, c->d_doc_total, key[0], idx[0]);
+        ONI_IDX(radix_sort_pairs(key, idx, counts, totals, D, 8, c->sm_count, s, &cur, &c->launches));
+        narrow_kernel<<<grid, 256, 0, s>>>(idx[cur], D, c->d_order);
+        c->launches += 2;
     }
-    // chunk lists
+    // pairs: pack, range-check, and sort by word id (stable: document order inside a word)
+    int32_t bad = 0;
+    if (nnz > 0) {
+        pack_tok_kernel<<<grid, 256, 0, s>>>(d_word, d_count, nnz, V, c->d_tok, key[0], idx[0], c->d_nan);
+        ONI_IDX_CUDA(cudaMemcpyAsync(&bad, c->d_nan, sizeof bad, cudaMemcpyDeviceToHost, s));
+        ONI_IDX(radix_sort_pairs(key, idx, counts, totals, nnz, 8, c->sm_count, s, &cur, &c->launches));
+        narrow_kernel<<<grid, 256, 0, s>>>(idx[cur], nnz, c->d_perm);
+        c->launches += 2;
+    }
+    word_ptr_kernel<<<(V + 256) / 256, 256, 0, s>>>(nnz > 0 ? key[cur] : key[0], nnz, V, d_wptr);
+    c->launches++;
+    std::vector<int64_t> wptr((size_t)V + 1);
+    ONI_IDX_CUDA(cudaMemcpyAsync(wptr.data(), d_wptr, sizeof(int64_t) * wptr.size(), cudaMemcpyDeviceToHost, s));
+    ONI_IDX_CUDA(cudaMemsetAsync(c->d_gamma, 0, sizeof(double) * (size_t)D * c->K, s));
+    ONI_IDX_CUDA(cudaMemsetAsync(c->d_doc_iters, 0, sizeof(int32_t) * (size_t)D, s));
+    ONI_IDX_CUDA(cudaStreamSynchronize(s));
+    ONI_IDX_CUDA(cudaMemsetAsync(c->d_nan, 0, sizeof(int32_t), s));
+    release();
+#undef ONI_IDX
+#undef ONI_IDX_CUDA
+    if (bad) return oni_set_error(ONI_ERR_ARG, "a word id lies outside [0,%d)", V);
+    tm.lap("device indexing");
+
+    // chunk lists of the deterministic reduction
     std::vector<SsItem> items, items2;
     int32_t n_partial = 0;
     for (int w = 0; w < V; w++) {
@@ -229,34 +290,14 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *ptr, co
             items2.push_back(SsItem{first, n_partial - first, w});
         }
     }
-
-    free_corpus(c);
-    c->D = D; c->nnz = nnz; c->n_long = n_long;
     c->n_items = (int32_t)items.size(); c->n_items2 = (int32_t)items2.size(); c->n_partial = n_partial;
-    ONI_TRY(dev_alloc(&c->d_tok, (size_t)nnz));
-    ONI_TRY(dev_alloc(&c->d_doc_ptr, (size_t)D + 1));
-    ONI_TRY(dev_alloc(&c->d_order, (size_t)D));
-    ONI_TRY(dev_alloc(&c->d_doc_total, (size_t)D));
-    ONI_TRY(dev_alloc(&c->d_perm, (size_t)nnz));
     ONI_TRY(dev_alloc(&c->d_items, items.size()));
     ONI_TRY(dev_alloc(&c->d_items2, items2.size()));
-    ONI_TRY(dev_alloc(&c->d_phi, (size_t)nnz * c->KP));
-    ONI_TRY(dev_alloc(&c->d_gamma, (size_t)D * c->K));
-    ONI_TRY(dev_alloc(&c->d_doc_lik, (size_t)D));
-    ONI_TRY(dev_alloc(&c->d_doc_ass, (size_t)D));
-    ONI_TRY(dev_alloc(&c->d_doc_iters, (size_t)D));
     ONI_TRY(dev_alloc(&c->d_partial, (size_t)n_partial * c->KP));
-    cudaStream_t s = c->stream;
-    ONI_CUDA(cudaMemcpyAsync(c->d_tok, tok.data(), sizeof(int2) * (size_t)nnz, cudaMemcpyHostToDevice, s));
-    ONI_CUDA(cudaMemcpyAsync(c->d_doc_ptr, ptr, sizeof(int64_t) * ((size_t)D + 1), cudaMemcpyHostToDevice, s));
-    ONI_CUDA(cudaMemcpyAsync(c->d_order, order.data(), sizeof(int32_t) * (size_t)D, cudaMemcpyHostToDevice, s));
-    ONI_CUDA(cudaMemcpyAsync(c->d_doc_total, total.data(), sizeof(double) * (size_t)D, cudaMemcpyHostToDevice, s));
-    ONI_CUDA(cudaMemcpyAsync(c->d_perm, perm.data(), sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, s));
     ONI_CUDA(cudaMemcpyAsync(c->d_items, items.data(), sizeof(SsItem) * items.size(), cudaMemcpyHostToDevice, s));
     ONI_CUDA(cudaMemcpyAsync(c->d_items2, items2.data(), sizeof(SsItem) * items2.size(), cudaMemcpyHostToDevice, s));
-    ONI_CUDA(cudaMemsetAsync(c->d_gamma, 0, sizeof(double) * (size_t)D * c->K, s));
-    ONI_CUDA(cudaMemsetAsync(c->d_doc_iters, 0, sizeof(int32_t) * (size_t)D, s));
     ONI_CUDA(cudaStreamSynchronize(s));  // host vectors die at return
+    tm.lap("chunk lists");
     return ONI_OK;
 }
 
@@ -374,24 +415,37 @@ extern "C" int oni_lda_set_corpus(oni_lda_ctx *c, int32_t D, int64_t nnz, const 
         return oni_set_error(ONI_ERR_ARG, "set_corpus: bad argument");
     ONI_CUDA(cudaSetDevice(c->device));
     c->estep_done = false;
-    return build_indices(c, D, nnz, ptr, word, count);
+    // stage the CSR arrays on the device, index there
+    StageTimer tm;
+    int64_t *d_ptr = nullptr;
+    int32_t *d_word = nullptr, *d_count = nullptr;
+    int rc = dev_alloc(&d_ptr, (size_t)D + 1);
+    if (rc == ONI_OK) rc = dev_alloc(&d_word, (size_t)nnz);
+    if (rc == ONI_OK) rc = dev_alloc(&d_count, (size_t)nnz);
+    if (rc == ONI_OK) {
+        cudaError_t e = cudaMemcpyAsync(d_ptr, ptr, sizeof(int64_t) * ((size_t)D + 1), cudaMemcpyHostToDevice, c->stream);
+        if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(d_word, word, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, c->stream);
+        if (e == cudaSuccess && nnz) e = cudaMemcpyAsync(d_count, count, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = oni_set_error(ONI_ERR_CUDA, "set_corpus upload: %s", cudaGetErrorString(e));
+    }
+    tm.lap("corpus upload");
+    if (rc == ONI_OK) rc = build_indices(c, D, nnz, ptr, d_ptr, d_word, d_count);
+    cudaFree(d_ptr); cudaFree(d_word); cudaFree(d_count);
+    return rc;
 }
 
 extern "C" int oni_lda_set_corpus_device(oni_lda_ctx *c, int32_t D, int64_t nnz,
                                          const int64_t *d_ptr, const int32_t *d_word,
                                          const int32_t *d_count)
 {
-    if (!c || !d_ptr || D < 0 || nnz < 0) return oni_set_error(ONI_ERR_ARG, "set_corpus_device: bad argument");
+    if (!c || !d_ptr || D < 0 || nnz < 0 || (nnz > 0 && (!d_word || !d_count)))
+        return oni_set_error(ONI_ERR_ARG, "set_corpus_device: bad argument");
     ONI_CUDA(cudaSetDevice(c->device));
     std::vector<int64_t> ptr((size_t)D + 1);
-    std::vector<int32_t> word((size_t)nnz), count((size_t)nnz);
     ONI_CUDA(cudaMemcpy(ptr.data(), d_ptr, sizeof(int64_t) * ((size_t)D + 1), cudaMemcpyDeviceToHost));
-    if (nnz) {
-        ONI_CUDA(cudaMemcpy(word.data(), d_word, sizeof(int32_t) * (size_t)nnz, cudaMemcpyDeviceToHost));
-        ONI_CUDA(cudaMemcpy(count.data(), d_count, sizeof(int32_t) * (size_t)nnz, cudaMemcpyDeviceToHost));
-    }
     c->estep_done = false;
-    return build_indices(c, D, nnz, ptr.data(), word.data(), count.data());
+    return build_indices(c, D, nnz, ptr.data(), d_ptr, d_word, d_count);
 }
 
 // Upload a topic-major host model into the word-major device table.

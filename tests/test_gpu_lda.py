@@ -229,3 +229,53 @@ def test_bad_arguments_are_rejected():
         bad = Corpus(np.array([0, 1], np.int64), np.array([10], np.int32), np.array([1], np.int32), 10)
         with pytest.raises(_lib.OniError):
             eng.set_corpus(bad)  # word id out of range
+
+
+def test_flow_day_size_invariants():
+    """BASELINE configs[1] at full size (1M documents, 50k words, ~55M pairs, K=20): the
+    oracle cannot run this in seconds, so the check is through size-independent
+    properties of two EM iterations: sum_k gamma_dk = K*alpha + total_d, exp(beta)
+    rows sum to 1, the bound increases, per-document bounds add up to the reduced
+    total, the reductions are bit-reproducible across runs, and a 20k-document
+    sample of documents matches the oracle's per-document inference."""
+    import torch
+    ptr, word, count = synth_corpus(1_000_000, 50_000, mu=3.5, seed=20160123, device="cuda", as_torch=True)
+    st = _lib.Settings(20, 1e-6, 20, 1e-6, 1)
+    runs = []
+    for _ in range(2):
+        with lda.LdaEngine(0, 20, 50_000, st) as eng:
+            eng.set_corpus_device(ptr, word, count)
+            eng.init_random(4357, 2.5)
+            lb0 = eng.logbeta() if not runs else None
+            lik1, _ = eng.em_iteration()
+            gam1 = eng.gamma()
+            doc_lik = eng.doc_likelihood()
+            lb1, a1 = eng.logbeta(), eng.alpha()
+            lik2, conv2 = eng.em_iteration()
+            runs.append((lik1, lik2, gam1, lb1, a1))
+            if lb0 is not None:
+                keep = (lb0, doc_lik)
+    (lik1, lik2, gam1, lb1, a1), other = runs
+    assert lik1 == other[0] and lik2 == other[1] and a1 == other[4]
+    assert np.array_equal(gam1, other[2]) and np.array_equal(lb1, other[3])
+    assert lik2 > lik1 and 0 < conv2 < 1
+    lb0, doc_lik = keep
+    assert abs(doc_lik.sum() - lik1) < 1e-9 * abs(lik1)
+    h_ptr, h_count = ptr.cpu().numpy(), count.cpu().numpy()
+    tot = np.add.reduceat(h_count.astype(np.float64), h_ptr[:-1])
+    assert np.allclose(gam1.sum(1), 20 * 2.5 + tot, rtol=1e-12)
+    assert np.allclose(np.exp(lb1).sum(1), 1.0, rtol=1e-9)
+    # oracle on a sample of documents (including the longest ones)
+    lens = np.diff(h_ptr)
+    pick = np.unique(np.concatenate([np.argsort(lens)[-20:], np.arange(0, 1_000_000, 50)]))
+    h_word = word.cpu().numpy()
+    L = pyoracle.lib()
+    worst = 0.0
+    for d in pick:
+        a, b = int(h_ptr[d]), int(h_ptr[d + 1])
+        g = np.zeros(20); phi = np.zeros((max(b - a, 1), 20))
+        lk = L.orc_doc_inference(b - a, np.ascontiguousarray(h_word[a:b]), np.ascontiguousarray(h_count[a:b]),
+                                 int(h_count[a:b].sum()), 20, 50_000, 2.5, lb0, 20, float(np.float32(1e-6)),
+                                 g, phi, None)
+        worst = max(worst, float(np.max(np.abs(gam1[d] - g) / g)), abs(doc_lik[d] - lk) / abs(lk))
+    assert worst < 1e-8, worst
