@@ -309,7 +309,7 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
             for (int t = 0; t < T; t++) {
                 const bool ok = (t < T - 1) || last_ok;
                 gs += ok ? gam[t] : 0.0;
-                part += ok ? lgamma(gam[t]) : 0.0;
+                part += ok ? lgamma_pos(gam[t], tabs.lg) : 0.0;
             }
             part += acc_b - acc_a;
 #pragma unroll
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
                 gs += __shfl_xor_sync(gmask, gs, o);
                 part += __shfl_xor_sync(gmask, part, o);
             }
-            const double lik = (lik_const - lgamma(gs)) + part + (SHIFT ? acc_s : 0.0);
+            const double lik = (lik_const - lgamma_pos(gs, tabs.lg)) + part + (SHIFT ? acc_s : 0.0);
             pass++;
             // lda-inference.c:79-80 and the loop condition :46-47
             const double conv = (lik_old - lik) / lik_old;

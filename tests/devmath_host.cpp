@@ -53,6 +53,16 @@ int main(void)
         if (drel > worst_dg) worst_dg = drel;
         if (d > worst_dg_abs && g > 0.05) worst_dg_abs = d;
     }
+    double worst_lg = 0;
+    for (int i = 0; i < 1000000; i++) {
+        double g = exp(-7.0 + 30.0 * urand());  // 1e-3 .. 1e10
+        long double want = lgammal((long double)g);
+        double d = fabs((double)((long double)oni::lgamma_pos(g, T.lg) - want));
+        // error relative to the size of the Stirling intermediates (what the bound sums)
+        double scale = fmax(fabs((double)want), fmax(g * log(g + 12.0), 20.0));
+        if (d / scale > worst_lg) worst_lg = d / scale;
+    }
+    printf("lgamma_max_rel %.3e\n", worst_lg);
     // flush and edge behaviour
     int edge_ok = oni::exp_tab(-708.5, T.ex) == 0.0 && oni::exp_tab(-1e6, T.ex) == 0.0 &&
                   oni::exp_tab(0.0, T.ex) == 1.0 && oni::log_tab(1.0, T.lg) == 0.0;

@@ -18,6 +18,7 @@ def test_devmath_accuracy_on_host(tmp_path):
     assert float(vals["exp_max_ulp"]) < 1.5
     assert float(vals["log_max_rel"]) < 4e-15
     assert float(vals["digamma_max_rel"]) < 4e-15
+    assert float(vals["lgamma_max_rel"]) < 4e-15
     assert vals["edge_ok"] == "1"
 
 
