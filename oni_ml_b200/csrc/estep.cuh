@@ -136,6 +136,13 @@ __device__ __forceinline__ double group_max(double v, unsigned gmask)
 }
 
 // ---------------------------------------------------------------- the kernel
+// A group that reaches the end of its sweep waits up to this many word visits for the
+// other groups of its warp, so that their end-of-sweep sections (bound, convergence
+// test, refill) run together instead of one group at a time.  0 = never wait.
+#ifndef ONI_ESTEP_WAIT
+#define ONI_ESTEP_WAIT 256
+#endif
+
 // Resident blocks per SM the register allocation is tuned for (128-thread blocks).
 #ifndef ONI_ESTEP_MINB
 #define ONI_ESTEP_MINB 3
@@ -176,6 +183,7 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
     int2 tk = make_int2(0, 0);   // (word, count) of the pair at `pos`
     int2 tk1 = make_int2(0, 0);  // ... and of the visit after it
     bool have = false, exhausted = false;
+    int waited = 0;
 
     while (true) {
         if (!have && !exhausted) {
@@ -218,9 +226,8 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
             }
         }
         if (__all_sync(0xffffffffu, !have)) break;
-        if (!have) continue;
 
-        if (pos < end) {
+        if (have && pos < end) {
             // ---- one word visit (lda-inference.c:50-75)
             const double c = (double)tk.y;
             double *phrow = p.phi + (size_t)pos * KP;
@@ -302,7 +309,12 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
                 s_keep = 1.0; c_keep = 0.0;
             }
         }
-        if (pos == end) {
+        // groups still inside their sweep (every lane of the warp votes here)
+        const bool others_stepping =
+            (ONI_ESTEP_WAIT > 0) && __any_sync(0xffffffffu, have && pos < end);
+        if (have && pos == end && others_stepping && waited < ONI_ESTEP_WAIT) waited++;
+        else if (have && pos == end) {
+            waited = 0;
             // ---- end of a sweep: the bound (lda-inference.c:93-127, folded)
             double gs = 0.0, part = 0.0;
 #pragma unroll
