@@ -129,6 +129,12 @@ score_filter_kernel(int K, const double *__restrict__ theta, const double *__res
     }
 }
 
+// Two staged variants of this kernel were measured and dropped (profiles/r1_score.txt): rows
+// gathered into shared memory with cp.async (LDGSTS, consecutive lanes on consecutive 16-byte
+// pieces, double-buffered) ran at 37-40 ms per 250 M events, and with per-lane 160-byte TMA
+// bulk copies (UBLKCP + mbarrier) at 49 ms, against 28 ms for the direct gather above: the
+// first is short of warps at 45 KB of shared memory each, the second is bound by the TMA
+// request rate (one 160-byte request per ~14 cycles per SM).
 // src/dst score of the ranked survivors (what the Scala stage appends to a row).
 template <bool FLOW>
 __global__ void rescored_kernel(int K, const double *theta, const double *pwz, long long m,
@@ -294,14 +300,13 @@ extern "C" int oni_score_events_device(oni_score_ctx *c, int32_t is_flow, int64_
     if (c->cap == 0) ONI_TRY(reserve_survivors(c, std::max<unsigned long long>(1u << 20, (unsigned long long)n / 64)));
     for (int attempt = 0; attempt < 2; attempt++) {
         ONI_CUDA(cudaEventRecord(c->e0, c->stream));
+        unsigned long long *sk = (unsigned long long *)c->key[0].p, *si = (unsigned long long *)c->idx[0].p;
         if (is_flow)
             score_filter_kernel<true><<<blocks, 256, 0, c->stream>>>(
-                c->K, c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base,
-                (unsigned long long *)c->key[0].p, (unsigned long long *)c->idx[0].p, c->cap, c->d_counter);
+                c->K, c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         else
             score_filter_kernel<false><<<blocks, 256, 0, c->stream>>>(
-                c->K, c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base,
-                (unsigned long long *)c->key[0].p, (unsigned long long *)c->idx[0].p, c->cap, c->d_counter);
+                c->K, c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         c->launches++;
         ONI_CUDA(cudaEventRecord(c->e1, c->stream));
         unsigned long long total = 0;
