@@ -321,10 +321,15 @@ def _our_arm(args):
     ms_total = e0.elapsed_time(e1)
     launches = eng.stats()["kernel_launches"] - launches0
     t = torch.tensor([ms_total, float(tokens), float(nnz)], dtype=torch.float64, device=dev)
+    my_estep = statistics.mean(p[0] for p in per_step)
+    per_rank = [my_estep]
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         ms_total, tokens_all, nnz_all = float(tmax[0]), float(tsum[1]), float(tsum[2])
+        allr = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(allr, torch.tensor([my_estep], dtype=torch.float64, device=dev))
+        per_rank = [float(x[0]) for x in allr]
     else:
         tokens_all, nnz_all = float(tokens), float(nnz)
     value = tokens_all * args.steps / (ms_total * 1e-3)
@@ -394,6 +399,7 @@ def _our_arm(args):
         "breakdown_ms": {"estep_kernel": ms_estep, "suffstats": statistics.mean(p[1] for p in per_step),
                          "mstep": statistics.mean(p[2] for p in per_step)},
         "word_visits_per_step": visits,
+        "estep_ms_per_rank": [round(x, 2) for x in per_rank],
     }
     if world == 1 and not args.no_cpu_baseline:
         try:
