@@ -12,10 +12,13 @@
 #define _GNU_SOURCE
 #include <ctype.h>
 #include <errno.h>
+#include <math.h>
+#include <pthread.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include "../../include/oni_lda.h"
 
@@ -96,6 +99,117 @@ static inline const char *scan_int(const char *p, long long *out)
     return p;
 }
 
+/* Parallel path for the shape lda_pre.py writes (one document per line, lda_pre.py:94):
+ * the buffer is cut at newlines into one piece per thread, every thread parses its lines
+ * into its own arrays, and the pieces are concatenated in order.  A line that does not
+ * hold exactly "N" and N "w:c" tokens makes the piece report failure, and the caller falls
+ * back to the sequential parser below, which accepts any whitespace like fscanf does. */
+typedef struct {
+    const char *beg, *end;
+    int64_t *len;      /* pairs per document */
+    int32_t *word, *count;
+    size_t ndocs, npairs, cap_docs, cap_pairs;
+    long long nterms;
+    int ok;
+} parse_piece;
+
+static void *parse_lines(void *arg)
+{
+    parse_piece *pc = arg;
+    const char *p = pc->beg;
+    pc->ok = 1;
+    while (p < pc->end) {
+        while (p < pc->end && (*p == ' ' || *p == '\t' || *p == '\r')) p++;
+        if (p >= pc->end) break;
+        if (*p == '\n') { p++; continue; }  /* blank line */
+        long long n;
+        const char *q = scan_int(p, &n);
+        if (!q || n < 0) { pc->ok = 0; return NULL; }
+        p = q;
+        if (pc->ndocs == pc->cap_docs) {
+            pc->cap_docs = pc->cap_docs ? pc->cap_docs * 2 : 4096;
+            pc->len = realloc(pc->len, sizeof(int64_t) * pc->cap_docs);
+        }
+        if (pc->npairs + (size_t)n > pc->cap_pairs) {
+            while (pc->npairs + (size_t)n > pc->cap_pairs) pc->cap_pairs = pc->cap_pairs ? pc->cap_pairs * 2 : 65536;
+            pc->word = realloc(pc->word, sizeof(int32_t) * pc->cap_pairs);
+            pc->count = realloc(pc->count, sizeof(int32_t) * pc->cap_pairs);
+        }
+        if (!pc->len || !pc->word || !pc->count) { pc->ok = 0; return NULL; }
+        for (long long i = 0; i < n; i++) {
+            long long w, c;
+            while (*p == ' ' || *p == '\t') p++;
+            q = scan_int(p, &w);
+            if (!q || *q != ':' || w < 0 || w > 0x7ffffffe) { pc->ok = 0; return NULL; }
+            q = scan_int(q + 1, &c);
+            if (!q) { pc->ok = 0; return NULL; }
+            p = q;
+            pc->word[pc->npairs] = (int32_t)w;
+            pc->count[pc->npairs] = (int32_t)c;
+            pc->npairs++;
+            if (w >= pc->nterms) pc->nterms = w + 1;
+        }
+        while (*p == ' ' || *p == '\t' || *p == '\r') p++;
+        if (*p == '\n') p++;
+        else if (*p != 0) { pc->ok = 0; return NULL; }  /* more tokens on the line: not line-shaped */
+        pc->len[pc->ndocs++] = n;
+    }
+    return NULL;
+}
+
+static int read_corpus_parallel(char *buf, size_t len, oni_lda_corpus *out)
+{
+    enum { MAXT = 8 };
+    long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+    int nt = (int)(ncpu < 1 ? 1 : (ncpu > MAXT ? MAXT : ncpu));
+    if (len < ((size_t)1 << 20)) nt = 1;
+    parse_piece pc[MAXT];
+    pthread_t th[MAXT];
+    memset(pc, 0, sizeof pc);
+    const char *cut = buf;
+    for (int t = 0; t < nt; t++) {
+        pc[t].beg = cut;
+        const char *want = (t == nt - 1) ? buf + len : buf + (len / (size_t)nt) * (size_t)(t + 1);
+        if (want < cut) want = cut;
+        while (want < buf + len && *want != '\n') want++;
+        if (want < buf + len) want++;  /* the piece ends after its newline */
+        pc[t].end = cut = want;
+    }
+    for (int t = 0; t < nt; t++)
+        if (nt == 1 || pthread_create(&th[t], NULL, parse_lines, &pc[t]) != 0) { parse_lines(&pc[t]); th[t] = 0; }
+    int ok = 1;
+    size_t ndocs = 0, npairs = 0;
+    long long nterms = 0;
+    for (int t = 0; t < nt; t++) {
+        if (nt > 1 && th[t]) pthread_join(th[t], NULL);
+        ok &= pc[t].ok;
+        ndocs += pc[t].ndocs; npairs += pc[t].npairs;
+        if (pc[t].nterms > nterms) nterms = pc[t].nterms;
+    }
+    int rc = 1;  /* 1 = not line-shaped, use the sequential parser */
+    if (ok && ndocs <= 0x7fffffffu) {
+        int64_t *ptr = malloc(sizeof(int64_t) * (ndocs + 1));
+        int32_t *word = malloc(sizeof(int32_t) * (npairs ? npairs : 1));
+        int32_t *count = malloc(sizeof(int32_t) * (npairs ? npairs : 1));
+        if (ptr && word && count) {
+            size_t d = 0, k = 0;
+            ptr[0] = 0;
+            for (int t = 0; t < nt; t++) {
+                memcpy(word + k, pc[t].word, sizeof(int32_t) * pc[t].npairs);
+                memcpy(count + k, pc[t].count, sizeof(int32_t) * pc[t].npairs);
+                for (size_t i = 0; i < pc[t].ndocs; i++) { k += (size_t)pc[t].len[i]; ptr[++d] = (int64_t)k; }
+            }
+            out->num_docs = (int32_t)ndocs; out->num_terms = (int32_t)nterms; out->nnz = (int64_t)npairs;
+            out->doc_ptr = ptr; out->word = word; out->count = count;
+            rc = 0;
+        } else {
+            free(ptr); free(word); free(count);
+        }
+    }
+    for (int t = 0; t < nt; t++) { free(pc[t].len); free(pc[t].word); free(pc[t].count); }
+    return rc;
+}
+
 int oni_lda_read_corpus(const char *path, oni_lda_corpus *out)
 {
     if (!path || !out) return oni_set_error(ONI_ERR_ARG, "read_corpus: null argument");
@@ -103,7 +217,10 @@ int oni_lda_read_corpus(const char *path, oni_lda_corpus *out)
     size_t len = 0;
     char *buf = slurp(path, &len);
     if (!buf) return oni_set_error(ONI_ERR_IO, "cannot read corpus %s: %s", path, strerror(errno));
+    if (read_corpus_parallel(buf, len, out) == 0) { free(buf); return ONI_OK; }
+    memset(out, 0, sizeof *out);
 
+    /* sequential, whitespace-tolerant: "N" then N "w:c" tokens, lda-data.c:35-51 */
     /* pass 1: count documents and pairs so each array is allocated once */
     size_t ndocs = 0, npairs = 0;
     {
@@ -179,11 +296,137 @@ void oni_lda_free_corpus(oni_lda_corpus *c)
 }
 
 /* ----------------------------------------------------------------- writers */
-static FILE *open_out(const char *path)
+/* "%5.10f" without printf.  The reference prints every beta and gamma value with
+ * this format (lda-model.c:205, lda-estimate.c:97-100); at flow-day size that is
+ * 21 M values and printf's generic path dominates the whole run.  The conversion
+ * below is exact: v = m * 2^e with a 53-bit m, so m * 10^10 fits 128 bits and the
+ * 10-decimal value is that product shifted by e, rounded half to even on the true
+ * remainder -- the same digits glibc prints.  Anything outside the fast range
+ * (non-finite, |v| >= 2^62 / 1e10 ... or so small that the shift leaves 128 bits)
+ * goes through snprintf. */
+typedef unsigned __int128 u128;
+
+static inline int fmt_u64(char *out, unsigned long long v)
+{
+    char tmp[24];
+    int n = 0;
+    do { tmp[n++] = (char)('0' + v % 10); v /= 10; } while (v);
+    for (int i = 0; i < n; i++) out[i] = tmp[n - 1 - i];
+    return n;
+}
+
+/* writes the text of printf("%5.10f", v) at out (no terminator); returns its length */
+static int format_fixed10(char *out, double v)
+{
+    union { double d; unsigned long long u; } b;
+    b.d = v;
+    const int neg = (int)(b.u >> 63);
+    const int ex = (int)((b.u >> 52) & 0x7ff);
+    unsigned long long m = b.u & 0xfffffffffffffULL;
+    if (ex == 0x7ff) return snprintf(out, 64, "%5.10f", v);  /* inf / nan */
+    int e;                                                   /* v = m * 2^e */
+    if (ex == 0) e = -1074; else { m |= 1ULL << 52; e = ex - 1075; }
+    u128 scaled;  /* round(|v| * 1e10) */
+    if (e >= 0) {
+        if (e > 10) return snprintf(out, 64, "%5.10f", v);   /* |v| >= 2^63: rare, let libc do it */
+        scaled = ((u128)m * 10000000000ULL) << e;
+    } else {
+        const int sh = -e;
+        const u128 prod = (u128)m * 10000000000ULL;          /* < 2^87 */
+        if (sh >= 128) scaled = 0;                           /* |v| < 2^-75: rounds to zero */
+        else {
+            scaled = prod >> sh;
+            const u128 rem = prod & ((((u128)1) << sh) - 1);
+            const u128 half = ((u128)1) << (sh - 1);
+            if (rem > half || (rem == half && (scaled & 1))) scaled++;  /* half to even */
+        }
+    }
+    const unsigned long long ip = (unsigned long long)(scaled / 10000000000ULL);
+    unsigned long long fp = (unsigned long long)(scaled % 10000000000ULL);
+    int n = 0;
+    if (neg) out[n++] = '-';
+    n += fmt_u64(out + n, ip);
+    out[n++] = '.';
+    for (int i = 9; i >= 0; i--) { out[n + i] = (char)('0' + fp % 10); fp /= 10; }
+    n += 10;
+    return n;  /* always >= 12 characters, so the minimum width 5 never pads */
+}
+
+/* A matrix as text: rows [r0, r1), every value with `lead` before it (beta: a blank
+ * before every value; gamma: a blank between values), '\n' after each row. */
+typedef struct {
+    const double *a;
+    int cols, r0, r1, lead_first;
+    char *buf;
+    size_t len;
+} fmt_job;
+
+static void *fmt_rows(void *arg)
+{
+    fmt_job *j = arg;
+    char *p = j->buf;
+    for (int r = j->r0; r < j->r1; r++) {
+        const double *row = j->a + (size_t)r * j->cols;
+        for (int c = 0; c < j->cols; c++) {
+            if (c > 0 || j->lead_first) *p++ = ' ';
+            p += format_fixed10(p, row[c]);
+        }
+        *p++ = '\n';
+    }
+    j->len = (size_t)(p - j->buf);
+    return NULL;
+}
+
+static int write_matrix(const char *path, const double *a, int rows, int cols, int lead_first)
 {
     FILE *f = fopen(path, "w");
-    if (f) setvbuf(f, NULL, _IOFBF, 1 << 20);
-    return f;
+    if (!f) return oni_set_error(ONI_ERR_IO, "cannot write %s: %s", path, strerror(errno));
+    /* values the fast formatter hands to libc (non-finite, |v| >= 2^63) can be hundreds of
+     * characters long; a matrix holding any is written the plain way */
+    int plain = 0;
+    for (size_t i = 0, n = (size_t)rows * cols; i < n; i++)
+        if (!(fabs(a[i]) < 9.0e18)) { plain = 1; break; }
+    if (plain) {
+        setvbuf(f, NULL, _IOFBF, 1 << 20);
+        for (int r = 0; r < rows; r++) {
+            for (int c = 0; c < cols; c++)
+                fprintf(f, (c > 0 || lead_first) ? " %5.10f" : "%5.10f", a[(size_t)r * cols + c]);
+            fputc('\n', f);
+        }
+        if (fclose(f) != 0) return oni_set_error(ONI_ERR_IO, "write failed on %s", path);
+        return ONI_OK;
+    }
+    /* blocks of rows formatted by a few threads, written in order */
+    enum { MAXT = 8 };
+    const size_t per_value = 32;  /* sign + up to 19 digits + '.' + 10 + blank, generous */
+    const int block = (int)(((size_t)1 << 22) / ((size_t)cols * per_value + 1)) + 1;  /* ~4 MB of text */
+    long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+    int nt = (int)(ncpu < 1 ? 1 : (ncpu > MAXT ? MAXT : ncpu));
+    if (rows <= block) nt = 1;
+    fmt_job job[MAXT];
+    pthread_t th[MAXT];
+    int rc = ONI_OK;
+    for (int t = 0; t < nt; t++) {
+        job[t].buf = malloc((size_t)block * ((size_t)cols * per_value + 1));
+        if (!job[t].buf) { rc = oni_set_error(ONI_ERR_NOMEM, "save: out of memory"); nt = t; break; }
+    }
+    for (int r = 0; rc == ONI_OK && r < rows; ) {
+        int used = 0;
+        for (int t = 0; t < nt && r < rows; t++, used++) {
+            job[t].a = a; job[t].cols = cols; job[t].lead_first = lead_first;
+            job[t].r0 = r; job[t].r1 = r + block < rows ? r + block : rows;
+            r = job[t].r1;
+            if (nt == 1) fmt_rows(&job[t]);
+            else if (pthread_create(&th[t], NULL, fmt_rows, &job[t]) != 0) { fmt_rows(&job[t]); th[t] = 0; }
+        }
+        for (int t = 0; t < used; t++) {
+            if (nt > 1 && th[t]) pthread_join(th[t], NULL);
+            if (fwrite(job[t].buf, 1, job[t].len, f) != job[t].len) rc = oni_set_error(ONI_ERR_IO, "write failed on %s", path);
+        }
+    }
+    for (int t = 0; t < nt; t++) free(job[t].buf);
+    if (fclose(f) != 0 && rc == ONI_OK) rc = oni_set_error(ONI_ERR_IO, "write failed on %s", path);
+    return rc;
 }
 
 int oni_lda_save_model(const char *root, int32_t k, int32_t v, const double *logbeta, double alpha)
@@ -192,17 +435,11 @@ int oni_lda_save_model(const char *root, int32_t k, int32_t v, const double *log
     if (!root) return oni_set_error(ONI_ERR_ARG, "save_model: null root");
     if (logbeta) {
         snprintf(name, sizeof name, "%s.beta", root);
-        FILE *f = open_out(name);
-        if (!f) return oni_set_error(ONI_ERR_IO, "cannot write %s: %s", name, strerror(errno));
-        for (int32_t i = 0; i < k; i++) {
-            const double *row = logbeta + (size_t)i * v;
-            for (int32_t j = 0; j < v; j++) fprintf(f, " %5.10f", row[j]); /* lda-model.c:205 */
-            fputc('\n', f);
-        }
-        if (fclose(f) != 0) return oni_set_error(ONI_ERR_IO, "write failed on %s", name);
+        int rc = write_matrix(name, logbeta, k, v, 1); /* " %5.10f" per value, lda-model.c:205 */
+        if (rc != ONI_OK) return rc;
     }
     snprintf(name, sizeof name, "%s.other", root);
-    FILE *f = open_out(name);
+    FILE *f = fopen(name, "w");
     if (!f) return oni_set_error(ONI_ERR_IO, "cannot write %s: %s", name, strerror(errno));
     fprintf(f, "num_topics %d\n", k);   /* lda-model.c:213-215 */
     fprintf(f, "num_terms %d\n", v);
@@ -214,14 +451,15 @@ int oni_lda_save_model(const char *root, int32_t k, int32_t v, const double *log
 int oni_lda_save_gamma(const char *path, int32_t d, int32_t k, const double *gamma)
 {
     if (!path || !gamma) return oni_set_error(ONI_ERR_ARG, "save_gamma: null argument");
-    FILE *f = open_out(path);
-    if (!f) return oni_set_error(ONI_ERR_IO, "cannot write %s: %s", path, strerror(errno));
-    for (int32_t i = 0; i < d; i++) {
-        const double *row = gamma + (size_t)i * k;
-        fprintf(f, "%5.10f", row[0]);                                  /* lda-estimate.c:97 */
-        for (int32_t j = 1; j < k; j++) fprintf(f, " %5.10f", row[j]); /* :100 */
-        fputc('\n', f);
-    }
-    if (fclose(f) != 0) return oni_set_error(ONI_ERR_IO, "write failed on %s", path);
-    return ONI_OK;
+    /* "%5.10f" then " %5.10f" (lda-estimate.c:97-100) */
+    return write_matrix(path, gamma, d, k, 0);
+}
+
+/* Test hook: the fast formatter against the C library on one value. */
+int oni_internal_format_fixed10(double v, char *out64)
+{
+    if (!(fabs(v) < 9.0e18)) return -1;  /* the writer sends these through fprintf */
+    int n = format_fixed10(out64, v);
+    out64[n] = 0;
+    return n;
 }

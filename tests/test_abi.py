@@ -97,3 +97,41 @@ def test_cli_usage_and_errors(tmp_path):
     p = lda.run_cli(["est", "2.5", "20", str(tmp_path / "nosettings"), "1", "x", "random", str(tmp_path)],
                     check_rc=False)
     assert p.returncode == 2 and "cannot open settings" in p.stderr
+
+
+def test_fast_fixed10_formatter_is_exact():
+    """The writers print "%5.10f" with an exact 128-bit conversion instead of printf;
+    it must give printf's digits on ties, near-ties, tiny, negative and large values."""
+    import random
+    import struct
+    L = C.CDLL(_lib.LIB_PATH)
+    L.oni_internal_format_fixed10.argtypes = [C.c_double, C.c_char_p]
+    L.oni_internal_format_fixed10.restype = C.c_int
+    buf = C.create_string_buffer(128)
+    rnd = random.Random(1)
+    vals = [0.0, -0.0, 1.0, -1.0, 0.5e-10, 1.5e-10, 2.5e-10, 1e-11, -1e-11, 123456789.123456789, 1e15,
+            9.0e18 * 0.99, 5e-324, -5e-324, 2.5, -100.0, 0.12345678905, 0.12345678915, 1e-300,
+            0.99999999995, 0.999999999949999, 9.99999999995]
+    for _ in range(60000):
+        vals.append(rnd.choice([-1, 1]) * rnd.random() * 2.0 ** rnd.uniform(-40, 40))
+    for _ in range(40000):
+        v = (rnd.randrange(0, 10 ** 13) * 10 + 5) / 1e11  # ties at the 11th decimal and neighbours
+        vals += [v, float(np.nextafter(v, 0)), float(np.nextafter(v, 1e9))]
+    for _ in range(40000):
+        vals.append(struct.unpack("<d", struct.pack("<Q", rnd.getrandbits(64)))[0])
+    checked = 0
+    for v in vals:
+        n = L.oni_internal_format_fixed10(v, buf)
+        if n < 0:
+            assert not abs(v) < 9.0e18  # non-finite or huge: the writer uses fprintf for those
+            continue
+        assert buf.value.decode() == "%5.10f" % v, repr(v)
+        checked += 1
+    assert checked > 150000
+
+
+def test_writer_handles_nonfinite_and_huge(tmp_path):
+    g = np.array([[1.5, float("inf"), -2.0], [1e300, float("nan"), 0.0]])
+    lda.save_gamma(str(tmp_path / "g"), g)
+    want = "".join(" ".join("%5.10f" % v for v in row) + "\n" for row in g)
+    assert open(tmp_path / "g").read() == want
