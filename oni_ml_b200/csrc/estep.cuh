@@ -46,7 +46,7 @@
 
 namespace oni {
 
-// exp/log tables (3 KB), copied to shared memory by every block of the E-step
+// exp/log tables (6 KB), copied to shared memory by every block of the E-step
 static __device__ const MathTables g_math_tables = ONI_MATH_TABLES_INIT;
 
 // ------------------------------------------------------------ special functions
