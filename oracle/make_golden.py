@@ -55,6 +55,31 @@ def run_ref(model, settings_text, alpha, k, seed, nproc, keep, outdir):
             shutil.copy(os.path.join(out, name), os.path.join(outdir, name))
 
 
+def make_c1():
+    """BASELINE.json configs[0]: 10k IP documents, 5k-word vocabulary, K=20, alpha=2.5, one
+    rank.  The corpus is regenerated from its seed by the tests (too large to commit as
+    text); kept here are likelihood.dat, final.other, 000.other and every 50th row of
+    final.gamma / every 25th column of final.beta of the reference's run."""
+    c = synth_corpus(10000, 5000, k_true=20, mu=2.5, seed=20160123)
+    out = os.path.join(GOLD, "c1_k20")
+    with tempfile.TemporaryDirectory() as tmp:
+        model = os.path.join(tmp, "model.dat")
+        write_model_dat(model, c)
+        run_ref(model, SETTINGS_SHIPPED, "2.5", 20, 4357, 1,
+                ["000.other", "likelihood.dat", "final.other", "final.gamma", "final.beta"], out)
+    gam = np.loadtxt(os.path.join(out, "final.gamma"))
+    beta = np.loadtxt(os.path.join(out, "final.beta"))
+    np.savetxt(os.path.join(out, "final.gamma.rows50"), gam[::50], fmt="%.10f")
+    np.savetxt(os.path.join(out, "final.beta.cols25"), beta[:, ::25], fmt="%.10f")
+    os.remove(os.path.join(out, "final.gamma"))
+    os.remove(os.path.join(out, "final.beta"))
+    with open(os.path.join(out, "corpus.txt"), "w") as f:
+        f.write("synth_corpus(10000, 5000, k_true=20, mu=2.5, seed=20160123): %d docs %d pairs %d tokens\n"
+                % (c.num_docs, c.nnz, c.tokens))
+        f.write("crc word %d count %d ptr %d\n" % (int(c.word.astype(np.int64).sum()),
+                                                   int(c.count.astype(np.int64).sum()), int(c.doc_ptr.sum())))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     c = synth_corpus(400, 300, k_true=8, mu=2.0, seed=20160122)
@@ -83,6 +108,7 @@ def main():
             os.path.join(GOLD, "c0_k5_fixed"))
     run_ref(model, SETTINGS_UNBOUNDED, "1.0", 37, 12345, 1,
             ["likelihood.dat", "final.other"], os.path.join(GOLD, "c0_k37_unbounded"))
+    make_c1()
     print("golden fixtures written to", GOLD)
 
 

@@ -279,3 +279,29 @@ def test_flow_day_size_invariants():
                                  g, phi, None)
         worst = max(worst, float(np.max(np.abs(gam1[d] - g) / g)), abs(doc_lik[d] - lk) / abs(lk))
     assert worst < 1e-8, worst
+
+
+def test_config1_full_run_matches_reference_binary(golden_dir):
+    """BASELINE configs[0] end to end: 10k documents, 5k words, K=20, alpha 2.5, shipped
+    settings, 21 EM iterations -- against what the unmodified oni-lda-c wrote for the same
+    corpus and seed (tests/golden/c1_k20, oracle/make_golden.py): the whole likelihood
+    trajectory, alpha, every 50th row of final.gamma and every 25th column of final.beta."""
+    d = os.path.join(golden_dir, "c1_k20")
+    c = synth_corpus(10000, 5000, k_true=20, mu=2.5, seed=20160123)
+    crc = open(os.path.join(d, "corpus.txt")).read().splitlines()[1].split()
+    if (int(c.word.astype(np.int64).sum()), int(c.count.astype(np.int64).sum()), int(c.doc_ptr.sum())) != (
+            int(crc[2]), int(crc[4]), int(crc[6])):
+        pytest.skip("the synthetic generator draws differently on this torch build")
+    st = lda.read_settings(os.path.join(d, "settings.txt"))
+    r = lda.estimate(c, 20, float(np.float32(2.5)), st, 4357)
+    want = files.read_likelihood(os.path.join(d, "likelihood.dat"))
+    assert r["iters"] == want.shape[0] == 21
+    assert rel_err(r["lik"], want[:, 0]) < REL
+    o = files.read_other(os.path.join(d, "final.other"))
+    assert abs(r["alpha"] - o["alpha"]) < REL * o["alpha"] + 1e-10
+    gam = np.loadtxt(os.path.join(d, "final.gamma.rows50"))
+    assert np.max(np.abs(r["gamma"][::50] - gam) / (np.abs(gam) + 1e-4)) < REL
+    beta = np.loadtxt(os.path.join(d, "final.beta.cols25"))
+    got = r["logbeta"][:, ::25]
+    assert np.array_equal(np.round(got, 10) == -100.0, beta == -100.0)
+    assert np.max(np.abs(got - beta) / (np.abs(beta) + 1e-4)) < REL
