@@ -112,6 +112,7 @@ struct oni_lda_ctx {
     int32_t *d_perm = nullptr;
     SsItem *d_items = nullptr, *d_items2 = nullptr;
     int32_t n_items = 0, n_items2 = 0, n_partial = 0;
+    std::vector<int32_t> level_off;  // items2[level_off[l] .. level_off[l+1]) = level l+2 of the reduction
 
     // model + variational state
     double *d_logbeta_t = nullptr, *d_alpha = nullptr;
@@ -274,9 +275,15 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     if (bad) return oni_set_error(ONI_ERR_ARG, "a word id lies outside [0,%d)", V);
     tm.lap("device indexing");
 
-    // chunk lists of the deterministic reduction
+    // chunk lists of the deterministic reduction: level 1 cuts a word's pairs into chunks
+    // of <= SS_CHUNK; a word with several chunks has its partial rows reduced the same way
+    // by the next level, and so on until one row per word is left (a word holding 5 % of a
+    // flow-day corpus needs three levels instead of one warp adding 10^4 rows in sequence)
     std::vector<SsItem> items, items2;
+    std::vector<int32_t> level_off{0};
     int32_t n_partial = 0;
+    struct Pending { int w; int64_t first, n; };
+    std::vector<Pending> pending, next;
     for (int w = 0; w < V; w++) {
         const int64_t a = wptr[w], n = wptr[w + 1] - a;
         if (n <= SS_CHUNK) {
@@ -287,9 +294,27 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
                 items.push_back(SsItem{a + o, (int32_t)std::min<int64_t>(SS_CHUNK, n - o), ~n_partial});
                 n_partial++;
             }
-            items2.push_back(SsItem{first, n_partial - first, w});
+            pending.push_back(Pending{w, first, n_partial - first});
         }
     }
+    while (!pending.empty()) {
+        next.clear();
+        for (const Pending &pd : pending) {
+            if (pd.n <= SS_CHUNK) {
+                items2.push_back(SsItem{pd.first, (int32_t)pd.n, pd.w});
+            } else {
+                const int32_t first = n_partial;
+                for (int64_t o = 0; o < pd.n; o += SS_CHUNK) {
+                    items2.push_back(SsItem{pd.first + o, (int32_t)std::min<int64_t>(SS_CHUNK, pd.n - o), ~n_partial});
+                    n_partial++;
+                }
+                next.push_back(Pending{pd.w, first, n_partial - first});
+            }
+        }
+        level_off.push_back((int32_t)items2.size());
+        pending.swap(next);
+    }
+    c->level_off = level_off;
     c->n_items = (int32_t)items.size(); c->n_items2 = (int32_t)items2.size(); c->n_partial = n_partial;
     ONI_TRY(dev_alloc(&c->d_items, items.size()));
     ONI_TRY(dev_alloc(&c->d_items2, items2.size()));
@@ -311,10 +336,12 @@ void launch_ss(oni_lda_ctx *c)
             c->d_items, c->n_items, c->d_perm, c->d_tok, c->d_phi, c->d_ss, c->d_partial, c->K, c->KP);
         c->launches++;
     }
-    if (c->n_items2 > 0) {
-        const int blocks = (c->n_items2 + warps_per_block - 1) / warps_per_block;
+    for (size_t l = 0; l + 1 < c->level_off.size(); l++) {
+        const int32_t lo = c->level_off[l], n = c->level_off[l + 1] - lo;
+        if (n <= 0) continue;
+        const int blocks = (n + warps_per_block - 1) / warps_per_block;
         ss_rows_kernel<G, T, 2><<<blocks, 128, 0, c->stream>>>(
-            c->d_items2, c->n_items2, nullptr, nullptr, c->d_partial, c->d_ss, c->d_partial, c->K, c->KP);
+            c->d_items2 + lo, n, nullptr, nullptr, c->d_partial, c->d_ss, c->d_partial, c->K, c->KP);
         c->launches++;
     }
 }

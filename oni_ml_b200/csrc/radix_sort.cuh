@@ -68,23 +68,39 @@ radix_count_kernel(const unsigned long long *key, const unsigned long long *idx,
     counts[(size_t)threadIdx.x * ntiles + blockIdx.x] = sh[threadIdx.x];
 }
 
-// exclusive scan of counts (digit-major, length 256*ntiles), in place, one block.
-static __global__ void __launch_bounds__(1024) radix_scan_kernel(unsigned long long *counts, long long len)
+// Exclusive scan of counts (digit-major [256][ntiles]) in place: block d scans row d,
+// starting from the number of elements with a smaller digit (from the digit totals of
+// this pass).  256 blocks.
+static __global__ void __launch_bounds__(256)
+radix_scan_kernel(unsigned long long *counts, int ntiles, const unsigned long long *pass_totals)
 {
-    __shared__ unsigned long long part[1024];
-    const long long per = (len + 1023) / 1024;
-    const long long lo = min(len, (long long)threadIdx.x * per), hi = min(len, lo + per);
+    __shared__ unsigned long long part[256];
+    __shared__ unsigned long long base_sh;
+    const int d = blockIdx.x;
+    unsigned long long *row = counts + (size_t)d * ntiles;
+    // digits below d
+    unsigned long long b = (threadIdx.x < d) ? pass_totals[threadIdx.x] : 0ull;
+    part[threadIdx.x] = b;
+    __syncthreads();
+    for (int h = 128; h > 0; h >>= 1) {
+        if (threadIdx.x < h) part[threadIdx.x] += part[threadIdx.x + h];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) base_sh = part[0];
+    __syncthreads();
+    const int per = (ntiles + 255) / 256;
+    const int lo = min(ntiles, (int)threadIdx.x * per), hi = min(ntiles, lo + per);
     unsigned long long s = 0;
-    for (long long i = lo; i < hi; i++) s += counts[i];
+    for (int i = lo; i < hi; i++) s += row[i];
     part[threadIdx.x] = s;
     __syncthreads();
     if (threadIdx.x == 0) {
-        unsigned long long run = 0;
-        for (int i = 0; i < 1024; i++) { const unsigned long long t = part[i]; part[i] = run; run += t; }
+        unsigned long long run = base_sh;
+        for (int i = 0; i < 256; i++) { const unsigned long long t = part[i]; part[i] = run; run += t; }
     }
     __syncthreads();
     unsigned long long run = part[threadIdx.x];
-    for (long long i = lo; i < hi; i++) { const unsigned long long t = counts[i]; counts[i] = run; run += t; }
+    for (int i = lo; i < hi; i++) { const unsigned long long t = row[i]; row[i] = run; run += t; }
 }
 
 // Stable scatter of one pass.  A warp owns RS_ROUNDS*32 consecutive keys and
@@ -163,7 +179,7 @@ static inline int radix_sort_pairs(unsigned long long *const key[2], unsigned lo
         if (trivial) continue;  // every element has the same digit here
         const int in = *cur, out = *cur ^ 1;
         radix_count_kernel<<<ntiles, RS_THREADS, 0, s>>>(key[in], idx[in], n, pass, ntiles, counts);
-        radix_scan_kernel<<<1, 1024, 0, s>>>(counts, 256LL * ntiles);
+        radix_scan_kernel<<<256, 256, 0, s>>>(counts, ntiles, totals + (size_t)pass * 256);
         radix_scatter_kernel<<<ntiles, RS_THREADS, 0, s>>>(key[in], idx[in], key[out], idx[out], n, pass, ntiles, counts);
         if (launches) *launches += 3;
         *cur = out;

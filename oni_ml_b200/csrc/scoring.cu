@@ -335,32 +335,12 @@ extern "C" int oni_score_rank(oni_score_ctx *c, int64_t *n_survivors)
     if (n <= 1) return ONI_OK;
     cudaStream_t s = c->stream;
     ONI_CUDA(cudaEventRecord(c->e1, s));
-    ONI_CUDA(cudaMemsetAsync(c->d_totals, 0, sizeof(unsigned long long) * RS_MAX_PASSES * 256, s));
-    const int tblocks = (int)std::min<long long>((n + RS_THREADS - 1) / RS_THREADS, (long long)c->sm_count * 8);
-    radix_totals_kernel<<<tblocks, RS_THREADS, 0, s>>>((unsigned long long *)c->key[0].p,
-                                                        (unsigned long long *)c->idx[0].p, n, c->d_totals);
-    c->launches++;
-    std::vector<unsigned long long> totals((size_t)RS_MAX_PASSES * 256);
-    ONI_CUDA(cudaMemcpyAsync(totals.data(), c->d_totals, sizeof(unsigned long long) * totals.size(),
-                             cudaMemcpyDeviceToHost, s));
-    ONI_CUDA(cudaStreamSynchronize(s));
     const int ntiles = (int)((n + RS_TILE - 1) / RS_TILE);
     ONI_TRY(c->counts.reserve(sizeof(unsigned long long) * 256 * (size_t)ntiles));
-    for (int pass = 0; pass < RS_MAX_PASSES; pass++) {
-        bool trivial = false;
-        for (int d = 0; d < 256; d++)
-            if (totals[(size_t)pass * 256 + d] == (unsigned long long)n) { trivial = true; break; }
-        if (trivial) continue;  // every survivor has the same digit here
-        const int in = c->cur, out = c->cur ^ 1;
-        unsigned long long *kin = (unsigned long long *)c->key[in].p, *vin = (unsigned long long *)c->idx[in].p;
-        unsigned long long *kout = (unsigned long long *)c->key[out].p, *vout = (unsigned long long *)c->idx[out].p;
-        unsigned long long *cnt = (unsigned long long *)c->counts.p;
-        radix_count_kernel<<<ntiles, RS_THREADS, 0, s>>>(kin, vin, n, pass, ntiles, cnt);
-        radix_scan_kernel<<<1, 1024, 0, s>>>(cnt, 256LL * ntiles);
-        radix_scatter_kernel<<<ntiles, RS_THREADS, 0, s>>>(kin, vin, kout, vout, n, pass, ntiles, cnt);
-        c->launches += 3;
-        c->cur = out;
-    }
+    unsigned long long *key[2] = {(unsigned long long *)c->key[0].p, (unsigned long long *)c->key[1].p};
+    unsigned long long *idx[2] = {(unsigned long long *)c->idx[0].p, (unsigned long long *)c->idx[1].p};
+    ONI_TRY(radix_sort_pairs(key, idx, (unsigned long long *)c->counts.p, c->d_totals, n, 0, c->sm_count, s,
+                             &c->cur, &c->launches));
     ONI_CUDA(cudaEventRecord(c->e2, s));
     ONI_CUDA(cudaStreamSynchronize(s));
     ONI_CUDA(cudaGetLastError());
@@ -662,7 +642,7 @@ extern "C" int oni_score_flow_noalloc(int32_t device, int32_t K, const double *d
                 if (h_totals[pass * 256 + d] == (unsigned long long)m) { trivial = true; break; }
             if (trivial) continue;
             radix_count_kernel<<<ntiles, RS_THREADS, 0, s>>>(key[cur], idx[cur], m, pass, ntiles, counts);
-            radix_scan_kernel<<<1, 1024, 0, s>>>(counts, 256LL * ntiles);
+            radix_scan_kernel<<<256, 256, 0, s>>>(counts, ntiles, totals + (size_t)pass * 256);
             radix_scatter_kernel<<<ntiles, RS_THREADS, 0, s>>>(key[cur], idx[cur], key[cur ^ 1], idx[cur ^ 1], m,
                                                                pass, ntiles, counts);
             cur ^= 1;
