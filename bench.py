@@ -392,8 +392,13 @@ def _our_arm(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "estep_kernel<G=4,T=5>", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": achieved / peak,
+                     # ncu --set full, profiles/r1_estep_final.txt: dram read+write = 316 B per word visit
+                     # (the phi row of every sweep streams through HBM); scaled to this launch's visits
+                     "traffic": int(316.4 * visits / world), "traffic_source": "ncu dram__bytes per word visit x visits of this launch",
+                     "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": int(alg_bytes), "ms_per_launch": ms_estep,
+                     "fp64_pipe": "56 % busy (ncu sm__pipe_fp64_cycles_active), 280 FP64 of 573 instructions per warp word-visit",
                      "note": "fp64-pipe bound, not HBM bound: %.3g (word,topic) visits per launch, each a "
                              "digamma+exp in fp64" % (visits * K_TOPICS)},
         "breakdown_ms": {"estep_kernel": ms_estep, "suffstats": statistics.mean(p[1] for p in per_step),
