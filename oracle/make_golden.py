@@ -37,14 +37,14 @@ SETTINGS_UNBOUNDED = ("var max iter -1\nvar convergence 1e-6\nem max iter 4\n"
                       "em convergence 1e-4\nalpha estimate\n")  # cf. inf-settings.txt
 
 
-def run_ref(model, settings_text, alpha, k, seed, nproc, keep, outdir):
+def run_ref(model, settings_text, alpha, k, seed, nproc, keep, outdir, start="random"):
     with tempfile.TemporaryDirectory() as tmp:
         st = os.path.join(tmp, "settings.txt")
         with open(st, "w") as f:
             f.write(settings_text)
         out = os.path.join(tmp, "out")
         env = dict(os.environ, ONI_LDA_SEED=str(seed), ONI_MPI_NP=str(nproc))
-        subprocess.run([REF, "est", alpha, str(k), st, str(nproc), model, "random", out],
+        subprocess.run([REF, "est", alpha, str(k), st, str(nproc), model, start, out],
                        check=True, env=env, stdout=subprocess.DEVNULL)
         os.makedirs(outdir, exist_ok=True)
         with open(os.path.join(outdir, "settings.txt"), "w") as f:
@@ -108,6 +108,22 @@ def main():
             os.path.join(GOLD, "c0_k5_fixed"))
     run_ref(model, SETTINGS_UNBOUNDED, "1.0", 37, 12345, 1,
             ["likelihood.dat", "final.other"], os.path.join(GOLD, "c0_k37_unbounded"))
+    # the other two starts of lda-estimate.c:147-167 and `lda inf` (lda-estimate.c:358-388)
+    short = ("var max iter 20\nvar convergence 1e-6\nem max iter 3\nem convergence 1e-6\nalpha estimate\n")
+    run_ref(model, short, "2.5", 20, 777, 1, ["000.beta", "likelihood.dat", "final.other"],
+            os.path.join(GOLD, "c0_k20_seeded"), start="seeded")
+    run_ref(model, short, "2.5", 20, 1, 1, ["000.other", "likelihood.dat", "final.other"],
+            os.path.join(GOLD, "c0_k20_resume"), start=os.path.join(GOLD, "c0_k20", "final"))
+    inf_dir = os.path.join(GOLD, "c0_k20_inf")
+    os.makedirs(inf_dir, exist_ok=True)
+    with open(os.path.join(inf_dir, "settings.txt"), "w") as f:
+        f.write("var max iter -1\nvar convergence 1e-6\nem max iter 100\nem convergence 1e-4\nalpha estimate\n")
+    with tempfile.TemporaryDirectory() as tmp:
+        subprocess.run([REF, "inf", os.path.join(inf_dir, "settings.txt"), os.path.join(GOLD, "c0_k20", "final"),
+                        model, os.path.join(tmp, "c0")], check=True, stdout=subprocess.DEVNULL,
+                       env=dict(os.environ, ONI_MPI_NP="1"))
+        shutil.copy(os.path.join(tmp, "c0-lda-lhood.dat"), inf_dir)
+        shutil.copy(os.path.join(tmp, "c0-gamma.dat"), inf_dir)
     make_c1()
     print("golden fixtures written to", GOLD)
 

@@ -305,3 +305,44 @@ def test_config1_full_run_matches_reference_binary(golden_dir):
     got = r["logbeta"][:, ::25]
     assert np.array_equal(np.round(got, 10) == -100.0, beta == -100.0)
     assert np.max(np.abs(got - beta) / (np.abs(beta) + 1e-4)) < REL
+
+
+def _cli_est(golden_dir, tmp_path, case, start, seed):
+    d = os.path.join(golden_dir, case)
+    out = tmp_path / case
+    lda.run_cli(["est", "2.5", "20", os.path.join(d, "settings.txt"), "1",
+                 os.path.join(golden_dir, "c0_model.dat"), start, str(out)], seed=seed)
+    return d, out
+
+
+def test_cli_seeded_start_matches_reference(golden_dir, tmp_path):
+    """`seeded`: corpus_initialize_ss (lda-model.c:120-144) draws its documents from the same
+    MT19937 stream -> 000.beta byte-identical, trajectory within 1e-6."""
+    d, out = _cli_est(golden_dir, tmp_path, "c0_k20_seeded", "seeded", 777)
+    assert open(out / "000.beta").read() == open(os.path.join(d, "000.beta")).read()
+    got, want = files.read_likelihood(str(out / "likelihood.dat")), files.read_likelihood(os.path.join(d, "likelihood.dat"))
+    assert got.shape == want.shape and rel_err(got[:, 0], want[:, 0]) < REL
+    a, b = files.read_other(str(out / "final.other")), files.read_other(os.path.join(d, "final.other"))
+    assert abs(a["alpha"] - b["alpha"]) < REL * b["alpha"] + 1e-10
+
+
+def test_cli_resume_from_model_root_matches_reference(golden_dir, tmp_path):
+    """Start from <root>.beta/.other: beta and alpha are re-read through float
+    (load_lda_model, lda-model.c:220-251) and alpha comes from the file, not argv."""
+    d, out = _cli_est(golden_dir, tmp_path, "c0_k20_resume", os.path.join(golden_dir, "c0_k20", "final"), 1)
+    assert open(out / "000.other").read() == open(os.path.join(d, "000.other")).read()
+    got, want = files.read_likelihood(str(out / "likelihood.dat")), files.read_likelihood(os.path.join(d, "likelihood.dat"))
+    assert got.shape == want.shape and rel_err(got[:, 0], want[:, 0]) < REL
+    a, b = files.read_other(str(out / "final.other")), files.read_other(os.path.join(d, "final.other"))
+    assert abs(a["alpha"] - b["alpha"]) < REL * b["alpha"] + 1e-10
+
+
+def test_cli_inference_matches_reference_binary(golden_dir, tmp_path):
+    """`lda inf` against the reference's own <name>-lda-lhood.dat / <name>-gamma.dat."""
+    d = os.path.join(golden_dir, "c0_k20_inf")
+    lda.run_cli(["inf", os.path.join(d, "settings.txt"), os.path.join(golden_dir, "c0_k20", "final"),
+                 os.path.join(golden_dir, "c0_model.dat"), str(tmp_path / "c0")])
+    gam, want = files.read_matrix(str(tmp_path / "c0-gamma.dat")), files.read_matrix(os.path.join(d, "c0-gamma.dat"))
+    assert np.max(np.abs(gam - want) / (np.abs(want) + 1e-4)) < REL
+    lh, wl = np.loadtxt(str(tmp_path / "c0-lda-lhood.dat")), np.loadtxt(os.path.join(d, "c0-lda-lhood.dat"))
+    assert np.allclose(lh, wl, rtol=REL, atol=2e-5)  # printed with 5 decimals (lda-estimate.c:387)
