@@ -93,7 +93,8 @@ int nccl_load()
 struct oni_lda_ctx {
     int device = 0;
     int K = 0, KP = 0, V = 0, G = 0, T = 0;
-    int T_long = 0;        // long documents run one per warp: G = 32, T_long topics per lane
+    int G_long = 32;       // long documents get wider groups: G_long lanes, T_long topics per lane
+    int T_long = 0;
     int long_min = 0;      // documents with at least this many pairs are "long" (0 = none)
     int32_t n_long = 0;    // they are the first n_long entries of `order`
     oni_lda_settings st{};
@@ -401,7 +402,10 @@ extern "C" int oni_lda_create(int32_t device, int32_t K, int32_t V, const oni_ld
     if (G < 32) {
         const char *env = getenv("ONI_LDA_LONG_DOC");
         c->long_min = env ? atoi(env) : 1024;
-        c->T_long = (K + 31) / 32;
+        const char *g = getenv("ONI_LDA_LONG_G");  // tuning knob: 8, 16 or 32
+        c->G_long = (g && (atoi(g) == 8 || atoi(g) == 16) && atoi(g) > G) ? atoi(g) : 32;
+        c->T_long = (K + c->G_long - 1) / c->G_long;
+        if (c->T_long > 8) { c->G_long = 32; c->T_long = (K + 31) / 32; }
     }
     ONI_TRY(dev_alloc(&c->d_logbeta_t, (size_t)V * c->KP));
     ONI_TRY(dev_alloc(&c->d_alpha, 1));
@@ -557,9 +561,9 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         EstepParams pl = p;
         pl.D = c->n_long;
         pl.ticket = c->d_ticket + 1;
-        cudaError_t e = launch_estep(32, c->T_long, shift, pl, c->sm_count, c->stream_long);
+        cudaError_t e = launch_estep(c->G_long, c->T_long, shift, pl, c->sm_count, c->stream_long);
         if (e != cudaSuccess)
-            return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=32,T=%d): %s", c->T_long, cudaGetErrorString(e));
+            return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=%d,T=%d): %s", c->G_long, c->T_long, cudaGetErrorString(e));
         c->launches++;
         ONI_CUDA(cudaEventRecord(c->ev_join, c->stream_long));
     }

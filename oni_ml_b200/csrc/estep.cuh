@@ -148,6 +148,11 @@ __device__ __forceinline__ double group_max(double v, unsigned gmask)
 #define ONI_ESTEP_WAIT 256
 #endif
 
+// Latency-tuned arithmetic in the one-document-per-warp instantiation (0 = off).
+#ifndef ONI_ESTEP_LAT
+#define ONI_ESTEP_LAT 1
+#endif
+
 // Resident blocks per SM the register allocation is tuned for (128-thread blocks).
 #ifndef ONI_ESTEP_MINB
 #define ONI_ESTEP_MINB 3
@@ -157,6 +162,10 @@ template <int G, int T, bool SHIFT>
 __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepParams p)
 {
     __shared__ MathTables tabs;
+    // one document per warp (G = 32): a long document is a serial chain of visits, so this
+    // instantiation trades a few instructions for a shorter dependency chain per visit
+    constexpr bool LAT = (G == 32) && (ONI_ESTEP_LAT != 0);
+    __shared__ double red_buf[LAT ? 4 * 32 : 1];  // per-warp exchange buffer of the sum below
     {
         const double *src = reinterpret_cast<const double *>(&g_math_tables);
         double *dst = reinterpret_cast<double *>(&tabs);
@@ -249,7 +258,7 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
                 if (fpos < end) prefetch_l2(reinterpret_cast<const char *>(p.phi + (size_t)fpos * KP) + j * 128);
             }
             const bool next_first_sweep = (pass == 0) && (npos != beg);
-            double lbn[T], oldn[T];
+            double lbn[T], oldn[T] = {};
             {
                 const double *nlb = p.logbeta_t + (size_t)tk1.x * KP;
                 const double *nph = p.phi + (size_t)npos * KP;
@@ -257,10 +266,18 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
                 for (int t = 0; t < T; t++) {
                     const int k = j + G * t;
                     const bool ok = (t < T - 1) || last_ok;
-                    lbn[t] = ok ? __ldg(nlb + k) : 0.0;
+                    if (LAT) {
+                        // unconditional loads from a clamped address: a select on the loaded
+                        // VALUE would wait for the load right here instead of one visit later
+                        // (20 % of a lone long document's time); the selects move to the use
+                        lbn[t] = __ldg(nlb + (ok ? k : 0));
+                        if (!next_first_sweep) oldn[t] = nph[ok ? k : 0];
+                    } else {
+                        lbn[t] = ok ? __ldg(nlb + k) : 0.0;
+                        oldn[t] = ok ? (next_first_sweep ? inv_k : nph[k]) : 0.0;
+                    }
                     // (a one-word document rereads the row this visit is about to write;
                     //  that case is patched below)
-                    oldn[t] = ok ? (next_first_sweep ? inv_k : nph[k]) : 0.0;
                 }
             }
             double x[T];
@@ -282,18 +299,44 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
                 x[t] = ((t < T - 1) || last_ok) ? e : 0.0;
                 s += x[t];
             }
-            s = group_sum<G>(s, gmask);
+            if (LAT) {
+                // all 32 partial sums through shared memory and a register tree: one LDS
+                // latency + 5 add levels instead of 5 shuffle+add levels
+                double *rb = red_buf + (threadIdx.x >> 5) * 32;
+                rb[lane] = s;
+                __syncwarp();
+                double v[32];
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    const double2 two = reinterpret_cast<const double2 *>(rb)[i];
+                    v[2 * i] = two.x; v[2 * i + 1] = two.y;
+                }
+#pragma unroll
+                for (int w = 16; w > 0; w >>= 1)
+#pragma unroll
+                    for (int i = 0; i < w; i++) v[i] += v[i + w];
+                s = v[0];
+                __syncwarp();
+            } else {
+                s = group_sum<G>(s, gmask);
+            }
             const double rs = rcp_pos(s);
             double a = 0.0;
 #pragma unroll
             for (int t = 0; t < T; t++) {
                 const double ph = x[t] * rs;
                 a = fma(ph, dg[t], a);
-                gam[t] = fma(c, ph - oldc[t], gam[t]);  // lda-inference.c:69-70
+                // old phi: 1/K during the first sweep (lda-inference.c:42), else the row loaded
+                // one visit ahead; nothing for a topic slot beyond K
+                const bool ok = (t < T - 1) || last_ok;
+                const double old = LAT ? (ok ? ((pass == 0) ? inv_k : oldc[t]) : 0.0) : oldc[t];
+                if (LAT) gam[t] = fma(c * x[t], rs, fma(-c, old, gam[t]));  // same value, one op after rs
+                else gam[t] = fma(c, ph - old, gam[t]);                     // lda-inference.c:69-70
                 x[t] = ph;
             }
 #pragma unroll
-            for (int t = 0; t < T; t++) dg[t] = digamma_ref(gam[t], tabs.lg);
+            for (int t = 0; t < T; t++)
+                dg[t] = LAT ? digamma_ref_lat(gam[t], tabs.lg) : digamma_ref(gam[t], tabs.lg);
 #pragma unroll
             for (int t = 0; t < T; t++)
                 if ((t < T - 1) || last_ok) phrow[j + G * t] = x[t];

@@ -8,7 +8,7 @@
 
 namespace oni {
 
-// Instantiated: G = 1 and G = 32 with T = 1..8; G in {2,4,8,16} with T = 5..8.
+// Instantiated: G in {1,8,16,32} with T = 1..8; G in {2,4} with T = 5..8.
 // Returns cudaErrorInvalidValue for anything else.
 cudaError_t launch_estep(int G, int T, bool shift, const EstepParams &p, int sm_count,
                          cudaStream_t stream);
