@@ -561,7 +561,7 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         EstepParams pl = p;
         pl.D = c->n_long;
         pl.ticket = c->d_ticket + 1;
-        cudaError_t e = launch_estep(c->G_long, c->T_long, shift, pl, c->sm_count, c->stream_long);
+        cudaError_t e = launch_estep(c->G_long, c->T_long, shift, pl, c->sm_count, c->stream_long, /*longdoc=*/true);
         if (e != cudaSuccess)
             return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=%d,T=%d): %s", c->G_long, c->T_long, cudaGetErrorString(e));
         c->launches++;

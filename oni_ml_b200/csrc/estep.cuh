@@ -158,13 +158,14 @@ __device__ __forceinline__ double group_max(double v, unsigned gmask)
 #define ONI_ESTEP_MINB 3
 #endif
 
-template <int G, int T, bool SHIFT>
+template <int G, int T, bool SHIFT, bool LONGDOC = false>
 __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepParams p)
 {
     __shared__ MathTables tabs;
     // one document per warp (G = 32): a long document is a serial chain of visits, so this
     // instantiation trades a few instructions for a shorter dependency chain per visit
-    constexpr bool LAT = (G == 32) && (ONI_ESTEP_LAT != 0);
+    // (LONGDOC launches hold only documents of >= 1024 pairs)
+    constexpr bool LAT = LONGDOC && (G == 32) && (ONI_ESTEP_LAT != 0);
     __shared__ double red_buf[LAT ? 4 * 32 : 1];  // per-warp exchange buffer of the sum below
     {
         const double *src = reinterpret_cast<const double *>(&g_math_tables);
@@ -346,7 +347,10 @@ __global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepP
                 lbc[t] = lbn[t];
                 oldc[t] = oldn[t];
             }
-            if (npos == pos) {  // one-word document: the row just written is the next "old"
+            // one-word document: the row just written is the next "old".  (Compiled out of the
+            // long-document kernel: it becomes a select on the in-flight load and cost a lone
+            // long document a quarter of its time.)
+            if (!LONGDOC && npos == pos) {
 #pragma unroll
                 for (int t = 0; t < T; t++) oldc[t] = x[t];
             }

@@ -10,8 +10,10 @@ namespace oni {
 
 // Instantiated: G in {1,8,16,32} with T = 1..8; G in {2,4} with T = 5..8.
 // Returns cudaErrorInvalidValue for anything else.
+// longdoc = the launch holds only long documents (>= 1024 pairs): selects the latency-tuned
+// build of the G = 32 kernel (T <= 4), otherwise ignored.
 cudaError_t launch_estep(int G, int T, bool shift, const EstepParams &p, int sm_count,
-                         cudaStream_t stream);
+                         cudaStream_t stream, bool longdoc = false);
 
 cudaError_t launch_estep_g1(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 cudaError_t launch_estep_g2(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
@@ -19,5 +21,6 @@ cudaError_t launch_estep_g4(int T, bool shift, const EstepParams &p, int sm_coun
 cudaError_t launch_estep_g8(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 cudaError_t launch_estep_g16(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 cudaError_t launch_estep_g32(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
+cudaError_t launch_estep_g32_long(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 
 }  // namespace oni
