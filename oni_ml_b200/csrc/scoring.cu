@@ -129,6 +129,100 @@ score_filter_kernel(int K, const double *__restrict__ theta, const double *__res
     }
 }
 
+// ---- paired variant (K = 2*CH, CH 16-byte pieces per row) -------------------------------
+// The kernel above is bound by the L1 data pipe, not by HBM: each lane of a 16-byte load
+// touches a different row, so a warp load is 32 half-used 32-byte sectors (ncu: lsu
+// wavefronts 96 % of peak, lts 78 %, dram 31 %).  Here lanes 2m and 2m+1 share their two
+// events: for every row, the even lane loads the even 16-byte pieces and the odd lane the
+// odd ones, so the pair reads whole 32-byte sectors, and one shuffle per piece hands the
+// pieces to the lane that owns the event.  Half the sectors per load, every sector requested
+// once; the sum itself is unchanged (one lane, topics in order, unfused).
+template <int CH>
+__device__ __forceinline__ double dot_paired(const double *theta, const double *pwz, int32_t my_doc,
+                                             int32_t my_word, double dflt, int lane)
+{
+    constexpr int HALF = (CH + 1) / 2;  // pieces per lane and row (the odd lane may hold one less)
+    const int q = lane & 1;
+    const int32_t pal_doc = __shfl_xor_sync(0xffffffffu, my_doc, 1);
+    const int32_t pal_word = __shfl_xor_sync(0xffffffffu, my_word, 1);
+    // rows of the even lane's event ("r0") and of the odd lane's event ("r1")
+    const int32_t d0 = q ? pal_doc : my_doc, w0 = q ? pal_word : my_word;
+    const int32_t d1 = q ? my_doc : pal_doc, w1 = q ? my_word : pal_word;
+    const double2 fill = make_double2(dflt, dflt);
+    double2 t0[HALF], p0[HALF], t1[HALF], p1[HALF];
+#pragma unroll
+    for (int i = 0; i < HALF; i++) {
+        const int piece = 2 * i + q;  // this lane's pieces: q, q+2, ...
+        const bool in = piece < CH;
+        t0[i] = (in && d0 >= 0) ? __ldg(reinterpret_cast<const double2 *>(theta + (size_t)d0 * (2 * CH)) + piece) : fill;
+        p0[i] = (in && w0 >= 0) ? __ldg(reinterpret_cast<const double2 *>(pwz + (size_t)w0 * (2 * CH)) + piece) : fill;
+        t1[i] = (in && d1 >= 0) ? __ldg(reinterpret_cast<const double2 *>(theta + (size_t)d1 * (2 * CH)) + piece) : fill;
+        p1[i] = (in && w1 >= 0) ? __ldg(reinterpret_cast<const double2 *>(pwz + (size_t)w1 * (2 * CH)) + piece) : fill;
+    }
+    // hand over: the even lane gives away its pieces of event 1 and receives the odd pieces
+    // of event 0; the odd lane the other way round
+    double2 mt[HALF], mp[HALF], ot[HALF], op[HALF];  // mine (kept), other (received)
+#pragma unroll
+    for (int i = 0; i < HALF; i++) {
+        const double2 give_t = q ? t0[i] : t1[i], give_p = q ? p0[i] : p1[i];
+        mt[i] = q ? t1[i] : t0[i];
+        mp[i] = q ? p1[i] : p0[i];
+        ot[i].x = __shfl_xor_sync(0xffffffffu, give_t.x, 1);
+        ot[i].y = __shfl_xor_sync(0xffffffffu, give_t.y, 1);
+        op[i].x = __shfl_xor_sync(0xffffffffu, give_p.x, 1);
+        op[i].y = __shfl_xor_sync(0xffffffffu, give_p.y, 1);
+    }
+    // topic order: piece 0, 1, 2, ...: even pieces sit with the even lane, odd with the odd one
+    double acc = 0.0;
+#pragma unroll
+    for (int piece = 0; piece < CH; piece++) {
+        const int i = piece >> 1;
+        const bool own = (piece & 1) == q;
+        const double2 a = own ? mt[i] : ot[i], b = own ? mp[i] : op[i];
+        acc = __dadd_rn(acc, __dmul_rn(a.x, b.x));
+        acc = __dadd_rn(acc, __dmul_rn(a.y, b.y));
+    }
+    return acc;
+}
+
+template <bool FLOW, int CH>
+__global__ void __launch_bounds__(256)
+score_filter_paired_kernel(const double *__restrict__ theta, const double *__restrict__ pwz, long long n,
+                           const int32_t *__restrict__ a_doc, const int32_t *__restrict__ b_doc,
+                           const int32_t *__restrict__ a_word, const int32_t *__restrict__ b_word,
+                           double dflt, double tol, long long idx_base, unsigned long long *surv_key,
+                           unsigned long long *surv_idx, unsigned long long cap,
+                           unsigned long long *counter)
+{
+    const int lane = threadIdx.x & 31;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long base = (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride) {
+        const long long e = base + lane;
+        const bool in = e < n;
+        // lanes past the end take part in the exchange with "missing" rows
+        const double sa = dot_paired<CH>(theta, pwz, in ? a_doc[e] : -1, in ? a_word[e] : -1, dflt, lane);
+        double key = sa;
+        if (FLOW) {
+            const double sb = dot_paired<CH>(theta, pwz, in ? b_doc[e] : -1, in ? b_word[e] : -1, dflt, lane);
+            key = (sb < sa) ? sb : sa;  // flow_post_lda.scala:238
+        }
+        const bool keep = in && (key < tol);  // strict, flow_post_lda.scala:245
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (m) {
+            unsigned long long pos = 0;
+            if (lane == __ffs(m) - 1) pos = atomicAdd(counter, (unsigned long long)__popc(m));
+            pos = __shfl_sync(0xffffffffu, pos, __ffs(m) - 1);
+            if (keep) {
+                pos += __popc(m & ((1u << lane) - 1u));
+                if (pos < cap) {
+                    surv_key[pos] = key_bits(key);
+                    surv_idx[pos] = (unsigned long long)(idx_base + e);
+                }
+            }
+        }
+    }
+}
+
 // Two staged variants of this kernel were measured and dropped (profiles/r1_score.txt): rows
 // gathered into shared memory with cp.async (LDGSTS, consecutive lanes on consecutive 16-byte
 // pieces, double-buffered) ran at 37-40 ms per 250 M events, and with per-lane 160-byte TMA
@@ -301,7 +395,16 @@ extern "C" int oni_score_events_device(oni_score_ctx *c, int32_t is_flow, int64_
     for (int attempt = 0; attempt < 2; attempt++) {
         ONI_CUDA(cudaEventRecord(c->e0, c->stream));
         unsigned long long *sk = (unsigned long long *)c->key[0].p, *si = (unsigned long long *)c->idx[0].p;
-        if (is_flow)
+        // K = 20 is what lda_post.py and both Scala stages hard-code (lda_post.py:115,
+        // flow_post_lda.scala:234): that case gets the lane-paired gather
+        const bool paired = (c->K == 20) && !getenv("ONI_SCORE_SIMPLE");
+        if (paired && is_flow)
+            score_filter_paired_kernel<true, 10><<<blocks, 256, 0, c->stream>>>(
+                c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
+        else if (paired)
+            score_filter_paired_kernel<false, 10><<<blocks, 256, 0, c->stream>>>(
+                c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
+        else if (is_flow)
             score_filter_kernel<true><<<blocks, 256, 0, c->stream>>>(
                 c->K, c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         else
