@@ -159,34 +159,34 @@ __device__ __forceinline__ double dot_paired(const double *theta, const double *
         t1[i] = (in && d1 >= 0) ? __ldg(reinterpret_cast<const double2 *>(theta + (size_t)d1 * (2 * CH)) + piece) : fill;
         p1[i] = (in && w1 >= 0) ? __ldg(reinterpret_cast<const double2 *>(pwz + (size_t)w1 * (2 * CH)) + piece) : fill;
     }
-    // hand over: the even lane gives away its pieces of event 1 and receives the odd pieces
-    // of event 0; the odd lane the other way round
-    double2 mt[HALF], mp[HALF], ot[HALF], op[HALF];  // mine (kept), other (received)
+    // hand over and accumulate, piece pair by piece pair: the even lane gives away its piece
+    // 2i of the odd lane's event and receives piece 2i+1 of its own; the odd lane the other way
+    // round.  After exchange i both lanes hold pieces 2i and 2i+1 of their own event, in topic
+    // order: (own, received) for the even lane, (received, own) for the odd one.
+    double acc = 0.0;
 #pragma unroll
     for (int i = 0; i < HALF; i++) {
         const double2 give_t = q ? t0[i] : t1[i], give_p = q ? p0[i] : p1[i];
-        mt[i] = q ? t1[i] : t0[i];
-        mp[i] = q ? p1[i] : p0[i];
-        ot[i].x = __shfl_xor_sync(0xffffffffu, give_t.x, 1);
-        ot[i].y = __shfl_xor_sync(0xffffffffu, give_t.y, 1);
-        op[i].x = __shfl_xor_sync(0xffffffffu, give_p.x, 1);
-        op[i].y = __shfl_xor_sync(0xffffffffu, give_p.y, 1);
-    }
-    // topic order: piece 0, 1, 2, ...: even pieces sit with the even lane, odd with the odd one
-    double acc = 0.0;
-#pragma unroll
-    for (int piece = 0; piece < CH; piece++) {
-        const int i = piece >> 1;
-        const bool own = (piece & 1) == q;
-        const double2 a = own ? mt[i] : ot[i], b = own ? mp[i] : op[i];
-        acc = __dadd_rn(acc, __dmul_rn(a.x, b.x));
-        acc = __dadd_rn(acc, __dmul_rn(a.y, b.y));
+        const double2 mine_t = q ? t1[i] : t0[i], mine_p = q ? p1[i] : p0[i];
+        double2 got_t, got_p;
+        got_t.x = __shfl_xor_sync(0xffffffffu, give_t.x, 1);
+        got_t.y = __shfl_xor_sync(0xffffffffu, give_t.y, 1);
+        got_p.x = __shfl_xor_sync(0xffffffffu, give_p.x, 1);
+        got_p.y = __shfl_xor_sync(0xffffffffu, give_p.y, 1);
+        const double2 a0 = q ? got_t : mine_t, b0 = q ? got_p : mine_p;  // piece 2i
+        const double2 a1 = q ? mine_t : got_t, b1 = q ? mine_p : got_p;  // piece 2i+1
+        acc = __dadd_rn(acc, __dmul_rn(a0.x, b0.x));
+        acc = __dadd_rn(acc, __dmul_rn(a0.y, b0.y));
+        if (2 * i + 1 < CH) {
+            acc = __dadd_rn(acc, __dmul_rn(a1.x, b1.x));
+            acc = __dadd_rn(acc, __dmul_rn(a1.y, b1.y));
+        }
     }
     return acc;
 }
 
 template <bool FLOW, int CH>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128, 4)
 score_filter_paired_kernel(const double *__restrict__ theta, const double *__restrict__ pwz, long long n,
                            const int32_t *__restrict__ a_doc, const int32_t *__restrict__ b_doc,
                            const int32_t *__restrict__ a_word, const int32_t *__restrict__ b_word,
@@ -203,7 +203,12 @@ score_filter_paired_kernel(const double *__restrict__ theta, const double *__res
         const double sa = dot_paired<CH>(theta, pwz, in ? a_doc[e] : -1, in ? a_word[e] : -1, dflt, lane);
         double key = sa;
         if (FLOW) {
-            const double sb = dot_paired<CH>(theta, pwz, in ? b_doc[e] : -1, in ? b_word[e] : -1, dflt, lane);
+            // (the second side's 2*CH loads must stay below the first side's sum: all 4*CH in
+            //  flight at once need 192 registers and leave 8 warps per SM; the compiler hoists
+            //  them over any barrier, so their addresses are made to depend on sa)
+            const int order = (sa != sa) ? 1 : 0;  // always 0: makes the addresses below depend on sa
+            const double sb = dot_paired<CH>(theta, pwz, in ? b_doc[e] + order : -1, in ? b_word[e] + order : -1,
+                                             dflt, lane);
             key = (sb < sa) ? sb : sa;  // flow_post_lda.scala:238
         }
         const bool keep = in && (key < tol);  // strict, flow_post_lda.scala:245
@@ -398,11 +403,12 @@ extern "C" int oni_score_events_device(oni_score_ctx *c, int32_t is_flow, int64_
         // K = 20 is what lda_post.py and both Scala stages hard-code (lda_post.py:115,
         // flow_post_lda.scala:234): that case gets the lane-paired gather
         const bool paired = (c->K == 20) && !getenv("ONI_SCORE_SIMPLE");
+        const int pblocks = (int)std::min<long long>((n + 127) / 128, (long long)c->sm_count * 32);
         if (paired && is_flow)
-            score_filter_paired_kernel<true, 10><<<blocks, 256, 0, c->stream>>>(
+            score_filter_paired_kernel<true, 10><<<pblocks, 128, 0, c->stream>>>(
                 c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         else if (paired)
-            score_filter_paired_kernel<false, 10><<<blocks, 256, 0, c->stream>>>(
+            score_filter_paired_kernel<false, 10><<<pblocks, 128, 0, c->stream>>>(
                 c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         else if (is_flow)
             score_filter_kernel<true><<<blocks, 256, 0, c->stream>>>(
