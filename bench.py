@@ -43,6 +43,15 @@ K_TOPICS = 20
 ALPHA = 2.5
 SEED = 4357
 WORKLOAD = dict(docs_per_gpu=1_000_000, vocab=50_000, mu=3.5, geom_p=0.25)
+# the other EM configurations of BASELINE.json (run with --shape; the default line is flow_day)
+SHAPES = {
+    "flow_day": dict(docs_per_gpu=1_000_000, vocab=50_000, mu=3.5, topics=20,
+                     name="flow day (BASELINE configs[1]): %d IP documents"),
+    "dns_day": dict(docs_total=2_000_000, vocab=100_000, mu=3.0, topics=20, dup_frac=0.0,
+                    name="DNS day (BASELINE configs[2]): 2M client-IP documents sharded over the GPUs, %d per GPU"),
+    "month": dict(docs_total=20_000_000, vocab=200_000, mu=3.5, topics=50,
+                  name="flow month-scale (BASELINE configs[3]): 20M documents over 8 GPUs, this run holds %d per GPU"),
+}
 SETTINGS_TXT = "var max iter 20\nvar convergence 1e-6\nem max iter %d\nem convergence 1e-6\nalpha estimate\n"
 
 
@@ -281,9 +290,16 @@ def _our_arm(args):
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
 
+    shape = SHAPES[args.shape]
+    global K_TOPICS
+    K_TOPICS = shape["topics"]
+    WORKLOAD["vocab"], WORKLOAD["mu"] = shape["vocab"], shape["mu"]
+    if "docs_total" in shape:  # fixed total: month-scale is defined on 8 GPUs, DNS day on the GPUs given
+        WORKLOAD["docs_per_gpu"] = shape["docs_total"] // (8 if args.shape == "month" else world)
     D, V = args.docs or WORKLOAD["docs_per_gpu"], WORKLOAD["vocab"]
     ptr, word, count = synth_corpus(D, V, k_true=K_TOPICS, mu=WORKLOAD["mu"], geom_p=WORKLOAD["geom_p"],
-                                    seed=20160123 + rank, device=dev, as_torch=True)
+                                    dup_frac=shape.get("dup_frac", 0.02), seed=20160123 + rank, device=dev,
+                                    as_torch=True)
     nnz = int(word.numel())
     tokens = int(count.sum(dtype=torch.int64))
     st = _lib.Settings(20, 1e-6, 10_000, 1e-6, 1)  # shipped thresholds; the loop count is ours
@@ -383,7 +399,10 @@ def _our_arm(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(world, {"pairs_per_gpu": nnz, "tokens_per_gpu": tokens}),
+        "config": workload_config(world, {"pairs_per_gpu": nnz, "tokens_per_gpu": tokens, "shape": args.shape,
+                                          "workload": (shape["name"] % D) + ", ~%.0fM (doc,word) pairs per GPU, %d-word "
+                                          "vocabulary, K=%d, alpha=%.1f, settings.txt as shipped; one step = one EM "
+                                          "iteration" % (nnz / 1e6, V, K_TOPICS, ALPHA)}),
         "em_iters_per_sec": args.steps / (ms_total * 1e-3),
         "pairs_per_sec": nnz_all * args.steps / (ms_total * 1e-3),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -391,7 +410,7 @@ def _our_arm(args):
                 "what": "LdaEngine from pinned host CSR: upload + index build + %d EM iterations + gamma/beta readback" % args.steps},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "estep_kernel<G=4,T=5>", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "estep_kernel<G=4,T=5>" if K_TOPICS == 20 else "estep_kernel (K=%d)" % K_TOPICS, "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak,
                      # ncu --set full, profiles/r1_estep_final.txt: dram read+write = 316 B per word visit
                      # (the phi row of every sweep streams through HBM); scaled to this launch's visits
@@ -503,7 +522,9 @@ def _score_arm(args):
                 "what": "oni_score_flow over host arrays (tables + event indices uploaded inside)"},
         "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / args.steps * 1e3,
         "roofline": {"bound": "hbm", "kernel": "score_filter_kernel<flow>", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": int(286.3 * n),
+                     "traffic_source": "ncu dram__bytes_read per event (profiles/r1_score.txt) x events",
+                     "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": n * (16 + 16 * K + 8), "ms_per_launch": statistics.mean(ms_score)},
         "breakdown_ms": {"score_filter": statistics.mean(ms_score), "rank": statistics.mean(ms_sort)},
         "ranked_list_identical_to_oracle_on_prefix": identical, "prefix_events": mp,
@@ -523,6 +544,8 @@ def main():
     ap.add_argument("--workload", default="em", choices=["em", "score"],
                     help="em (default, the headline metric) or score (BASELINE configs[4])")
     ap.add_argument("--events", type=int, default=250_000_000, help="events for --workload score")
+    ap.add_argument("--shape", default="flow_day", choices=sorted(SHAPES),
+                    help="EM corpus shape: flow_day (default, the headline), dns_day, month")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
