@@ -83,6 +83,14 @@ typedef struct {
 int oni_lda_read_corpus(const char *model_dat_path, oni_lda_corpus *out);
 void oni_lda_free_corpus(oni_lda_corpus *c);
 
+/* The corpus indexing stage, lda_pre.py (ml_ops.sh:67): reads <dir>doc_wc.dat
+ * ("ip,word,count" rows) and writes <dir>words.dat, <dir>doc.dat and <dir>model.dat
+ * byte for byte as the script does (word ids from 0 and document ids from 1 in order
+ * of first appearance, lda_pre.py:33-44,57-73; a word repeated inside a document stays
+ * a separate pair, :66; model.dat line = pair count then " w:c"..., :94).  `dir` is a
+ * prefix, used like the script's argv[1] ("path/"). */
+int oni_lda_pre(const char *dir);
+
 /* ------------------------------------------------------------------------ */
 /* Whole-run entry points                                                    */
 

@@ -69,6 +69,7 @@ SIGNATURES = {
     "oni_lda_read_settings": (C.c_int, [C.c_char_p, C.POINTER(Settings)]),
     "oni_lda_read_corpus": (C.c_int, [C.c_char_p, C.POINTER(CorpusC)]),
     "oni_lda_free_corpus": (None, [C.POINTER(CorpusC)]),
+    "oni_lda_pre": (C.c_int, [C.c_char_p]),
     "oni_lda_main": (C.c_int, [C.c_int, C.POINTER(C.c_char_p)]),
     "oni_lda_estimate": (C.c_int, [C.POINTER(CorpusC), _i32, _f64, C.POINTER(Settings), C.c_uint32,
                                    _i32, C.POINTER(ResultC)]),

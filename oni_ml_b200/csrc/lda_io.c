@@ -463,3 +463,165 @@ int oni_internal_format_fixed10(double v, char *out64)
     out64[n] = 0;
     return n;
 }
+
+/* ------------------------------------------------------------- lda_pre.py */
+/* The corpus indexing stage of the pipeline (lda_pre.py:30-94), byte-identical outputs:
+ *   <dir>doc_wc.dat  rows "ip,word,count"                       (input, ml_ops.sh:59-62)
+ *   <dir>words.dat   "<word id>,<word>"   ids from 0, first appearance   (lda_pre.py:33-44)
+ *   <dir>doc.dat     "<doc id>,<ip>"      ids from 1, first appearance   (lda_pre.py:57-73)
+ *   <dir>model.dat   "<pairs> w:c w:c ..." one line per document in doc.dat order; a word
+ *                    repeated inside a document stays a separate pair     (lda_pre.py:66-94)
+ * `dir` is used as a prefix exactly like the script's sys.argv[1] (ml_ops.sh passes "path/").
+ * Fields are split at commas; a field wrapped in double quotes may contain commas (the csv
+ * module's default dialect); the count is copied through as text. */
+static FILE *open_out(const char *path)
+{
+    FILE *f = fopen(path, "w");
+    if (f) setvbuf(f, NULL, _IOFBF, 1 << 20);
+    return f;
+}
+
+typedef struct { const char *s; uint32_t len; int32_t id; } pre_key;
+typedef struct { pre_key *slot; size_t cap, used; } pre_map;
+
+static uint64_t pre_hash(const char *s, uint32_t n)
+{
+    uint64_t h = 1469598103934665603ULL;
+    for (uint32_t i = 0; i < n; i++) { h ^= (unsigned char)s[i]; h *= 1099511628211ULL; }
+    return h;
+}
+
+static int pre_map_grow(pre_map *m)
+{
+    size_t ncap = m->cap ? m->cap * 2 : (1u << 16);
+    pre_key *ns = calloc(ncap, sizeof(pre_key));
+    if (!ns) return 0;
+    for (size_t i = 0; i < m->cap; i++)
+        if (m->slot[i].s) {
+            size_t j = pre_hash(m->slot[i].s, m->slot[i].len) & (ncap - 1);
+            while (ns[j].s) j = (j + 1) & (ncap - 1);
+            ns[j] = m->slot[i];
+        }
+    free(m->slot);
+    m->slot = ns; m->cap = ncap;
+    return 1;
+}
+
+/* id of the key, inserting it with id = next_id if new (*is_new says which) */
+static int32_t pre_map_get(pre_map *m, const char *s, uint32_t n, int32_t next_id, int *is_new)
+{
+    if ((m->used + 1) * 10 >= m->cap * 7 && !pre_map_grow(m)) return -1;
+    size_t j = pre_hash(s, n) & (m->cap - 1);
+    while (m->slot[j].s) {
+        if (m->slot[j].len == n && memcmp(m->slot[j].s, s, n) == 0) { *is_new = 0; return m->slot[j].id; }
+        j = (j + 1) & (m->cap - 1);
+    }
+    m->slot[j].s = s; m->slot[j].len = n; m->slot[j].id = next_id;
+    m->used++;
+    *is_new = 1;
+    return next_id;
+}
+
+/* one csv field starting at p (stops at ',' or end of line); returns the char after it */
+static const char *pre_field(const char *p, const char *eol, const char **fs, uint32_t *fl)
+{
+    if (p < eol && *p == '"') {
+        const char *q = p + 1;
+        while (q < eol && *q != '"') q++;
+        *fs = p + 1; *fl = (uint32_t)(q - p - 1);
+        p = (q < eol) ? q + 1 : q;
+        while (p < eol && *p != ',') p++;
+    } else {
+        const char *q = p;
+        while (q < eol && *q != ',') q++;
+        *fs = p; *fl = (uint32_t)(q - p);
+        p = q;
+    }
+    return (p < eol) ? p + 1 : p;
+}
+
+int oni_lda_pre(const char *dir)
+{
+    if (!dir) return oni_set_error(ONI_ERR_ARG, "lda_pre: null directory prefix");
+    char name[4096];
+    snprintf(name, sizeof name, "%sdoc_wc.dat", dir);
+    size_t len = 0;
+    char *buf = slurp(name, &len);
+    if (!buf) return oni_set_error(ONI_ERR_IO, "cannot read %s: %s", name, strerror(errno));
+    int rc = ONI_OK;
+    pre_map words = {0}, docs = {0};
+    size_t nrows = 0, cap_rows = 1 << 20;
+    int32_t *row_doc = malloc(sizeof(int32_t) * cap_rows), *row_word = malloc(sizeof(int32_t) * cap_rows);
+    const char **row_cnt = malloc(sizeof(char *) * cap_rows);
+    uint32_t *row_cnt_len = malloc(sizeof(uint32_t) * cap_rows);
+    FILE *fw = NULL, *fd = NULL, *fm = NULL;
+    int64_t *doc_ptr = NULL, *cursor = NULL;
+    uint32_t *order = NULL;
+    if (!row_doc || !row_word || !row_cnt || !row_cnt_len) { rc = oni_set_error(ONI_ERR_NOMEM, "lda_pre: out of memory"); goto done; }
+    snprintf(name, sizeof name, "%swords.dat", dir);
+    fw = open_out(name);
+    snprintf(name, sizeof name, "%sdoc.dat", dir);
+    fd = open_out(name);
+    if (!fw || !fd) { rc = oni_set_error(ONI_ERR_IO, "lda_pre: cannot write under %s: %s", dir, strerror(errno)); goto done; }
+    int32_t n_words = 0, n_docs = 0;
+    for (const char *p = buf, *end = buf + len; p < end;) {
+        const char *eol = memchr(p, '\n', (size_t)(end - p));
+        if (!eol) eol = end;
+        const char *line_end = (eol > p && eol[-1] == '\r') ? eol - 1 : eol;
+        if (line_end > p) {
+            const char *f[3]; uint32_t fl[3];
+            const char *q = p;
+            int nf = 0;
+            while (nf < 3) {  /* the first three fields; anything after them is ignored */
+                const int had_comma = (q > p && q[-1] == ',');
+                if (q >= line_end && !(nf > 0 && had_comma)) break;
+                q = pre_field(q, line_end, &f[nf], &fl[nf]);
+                nf++;
+            }
+            if (nf < 3) { rc = oni_set_error(ONI_ERR_IO, "doc_wc.dat row %zu: expected ip,word,count", nrows + 1); goto done; }
+            if (nrows == cap_rows) {
+                cap_rows *= 2;
+                row_doc = realloc(row_doc, sizeof(int32_t) * cap_rows); row_word = realloc(row_word, sizeof(int32_t) * cap_rows);
+                row_cnt = realloc(row_cnt, sizeof(char *) * cap_rows); row_cnt_len = realloc(row_cnt_len, sizeof(uint32_t) * cap_rows);
+                if (!row_doc || !row_word || !row_cnt || !row_cnt_len) { rc = oni_set_error(ONI_ERR_NOMEM, "lda_pre: out of memory"); goto done; }
+            }
+            int is_new;
+            int32_t w = pre_map_get(&words, f[1], fl[1], n_words, &is_new);
+            if (w < 0) { rc = oni_set_error(ONI_ERR_NOMEM, "lda_pre: out of memory"); goto done; }
+            if (is_new) { fprintf(fw, "%d,%.*s\n", w, (int)fl[1], f[1]); n_words++; }           /* lda_pre.py:40 */
+            int32_t d = pre_map_get(&docs, f[0], fl[0], n_docs + 1, &is_new);                       /* ids from 1, :61 */
+            if (d < 0) { rc = oni_set_error(ONI_ERR_NOMEM, "lda_pre: out of memory"); goto done; }
+            if (is_new) { fprintf(fd, "%d,%.*s\n", d, (int)fl[0], f[0]); n_docs++; }              /* :71 */
+            row_doc[nrows] = d - 1; row_word[nrows] = w; row_cnt[nrows] = f[2]; row_cnt_len[nrows] = fl[2];
+            nrows++;
+        }
+        p = eol + 1;
+    }
+    /* rows grouped by document, order of appearance kept (stable counting sort) */
+    doc_ptr = calloc((size_t)n_docs + 1, sizeof(int64_t));
+    cursor = malloc(sizeof(int64_t) * ((size_t)n_docs + 1));
+    order = malloc(sizeof(uint32_t) * (nrows ? nrows : 1));
+    if (!doc_ptr || !cursor || !order) { rc = oni_set_error(ONI_ERR_NOMEM, "lda_pre: out of memory"); goto done; }
+    for (size_t i = 0; i < nrows; i++) doc_ptr[row_doc[i] + 1]++;
+    for (int32_t d = 0; d < n_docs; d++) doc_ptr[d + 1] += doc_ptr[d];
+    memcpy(cursor, doc_ptr, sizeof(int64_t) * ((size_t)n_docs + 1));
+    for (size_t i = 0; i < nrows; i++) order[cursor[row_doc[i]]++] = (uint32_t)i;
+    snprintf(name, sizeof name, "%smodel.dat", dir);
+    fm = open_out(name);
+    if (!fm) { rc = oni_set_error(ONI_ERR_IO, "cannot write %s: %s", name, strerror(errno)); goto done; }
+    for (int32_t d = 0; d < n_docs; d++) {
+        fprintf(fm, "%lld", (long long)(doc_ptr[d + 1] - doc_ptr[d]));                             /* lda_pre.py:94 */
+        for (int64_t k = doc_ptr[d]; k < doc_ptr[d + 1]; k++) {
+            const uint32_t i = order[k];
+            fprintf(fm, " %d:%.*s", row_word[i], (int)row_cnt_len[i], row_cnt[i]);               /* :66 */
+        }
+        fputc('\n', fm);
+    }
+done:
+    if (fw && fclose(fw) != 0 && rc == ONI_OK) rc = oni_set_error(ONI_ERR_IO, "lda_pre: write failed (words.dat)");
+    if (fd && fclose(fd) != 0 && rc == ONI_OK) rc = oni_set_error(ONI_ERR_IO, "lda_pre: write failed (doc.dat)");
+    if (fm && fclose(fm) != 0 && rc == ONI_OK) rc = oni_set_error(ONI_ERR_IO, "lda_pre: write failed (model.dat)");
+    free(words.slot); free(docs.slot); free(row_doc); free(row_word); free(row_cnt); free(row_cnt_len);
+    free(doc_ptr); free(cursor); free(order); free(buf);
+    return rc;
+}

@@ -40,6 +40,11 @@ def read_corpus(path: str) -> Corpus:
         L.oni_lda_free_corpus(C.byref(c))
 
 
+def lda_pre(dir_prefix: str) -> None:
+    """lda_pre.py (ml_ops.sh:67) through the library: doc_wc.dat -> words.dat, doc.dat, model.dat."""
+    check(_lib.load().oni_lda_pre(dir_prefix.encode()))
+
+
 def _corpus_c(corpus: Corpus) -> _lib.CorpusC:
     ptr = np.ascontiguousarray(corpus.doc_ptr, dtype=np.int64)
     word = np.ascontiguousarray(corpus.word, dtype=np.int32)

@@ -80,6 +80,24 @@ def make_c1():
                                                    int(c.count.astype(np.int64).sum()), int(c.doc_ptr.sum())))
 
 
+def make_pre():
+    """lda_pre.py fixture: a doc_wc.dat shaped like flow_pre_lda.scala's output (ip,word,count;
+    words repeat inside a document, one field is quoted) and what the REFERENCE script
+    (/root/reference/lda_pre.py, runs unmodified under Python 3) writes for it."""
+    import random
+    rnd = random.Random(5)
+    out = os.path.join(GOLD, "pre")
+    os.makedirs(out, exist_ok=True)
+    words = ["%d.0_%d.0_%d.0_%d.0" % (rnd.randint(0, 65535), rnd.randint(0, 9), rnd.randint(0, 9), rnd.randint(0, 9))
+             for _ in range(120)] + ["-1_80.0_3.0_2.0_1.0", '"quoted,word"']
+    ips = ["10.%d.%d.%d" % (rnd.randint(0, 3), rnd.randint(0, 255), rnd.randint(0, 255)) for _ in range(80)]
+    rows = ["%s,%s,%d" % (rnd.choice(ips), rnd.choice(words), rnd.randint(1, 900)) for _ in range(1500)]
+    rows.append("10.9.9.9,solo_word,7")
+    with open(os.path.join(out, "doc_wc.dat"), "w") as f:
+        f.write("\n".join(rows) + "\n")
+    subprocess.run([sys.executable, "/root/reference/lda_pre.py", out + "/"], check=True, stdout=subprocess.DEVNULL)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     c = synth_corpus(400, 300, k_true=8, mu=2.0, seed=20160122)
@@ -125,6 +143,7 @@ def main():
         shutil.copy(os.path.join(tmp, "c0-lda-lhood.dat"), inf_dir)
         shutil.copy(os.path.join(tmp, "c0-gamma.dat"), inf_dir)
     make_c1()
+    make_pre()
     print("golden fixtures written to", GOLD)
 
 

@@ -135,3 +135,19 @@ def test_writer_handles_nonfinite_and_huge(tmp_path):
     lda.save_gamma(str(tmp_path / "g"), g)
     want = "".join(" ".join("%5.10f" % v for v in row) + "\n" for row in g)
     assert open(tmp_path / "g").read() == want
+
+
+def test_lda_pre_byte_identical_to_reference_script(tmp_path, golden_dir):
+    """oni_lda_pre against what the reference's lda_pre.py wrote for the same doc_wc.dat
+    (tests/golden/pre, oracle/make_golden.py): index mappings must be bit-exact."""
+    import shutil
+    src = os.path.join(golden_dir, "pre")
+    shutil.copy(os.path.join(src, "doc_wc.dat"), tmp_path / "doc_wc.dat")
+    lda.lda_pre(str(tmp_path) + "/")
+    for name in ("words.dat", "doc.dat", "model.dat"):
+        assert open(tmp_path / name, "rb").read() == open(os.path.join(src, name), "rb").read(), name
+    # and the model.dat it wrote parses back to the same pairs (repeated words kept)
+    c = lda.read_corpus(str(tmp_path / "model.dat"))
+    assert c.nnz == 1501 and c.num_docs == len(open(tmp_path / "doc.dat").readlines())
+    with pytest.raises(_lib.OniError):
+        lda.lda_pre(str(tmp_path / "nowhere") + "/")
