@@ -316,6 +316,14 @@ int oni_lda_post(int32_t device, int32_t num_docs, int32_t num_topics, int32_t n
                  const double *gamma, const double *logbeta, int32_t text_digits,
                  double *theta /* [D][K] */, double *pwz /* [V][K] */);
 
+/* lda_post.py as a whole (ml_ops.sh:84): reads <dir>final.gamma, final.beta, doc.dat and
+ * words.dat, writes <dir>doc_results.csv ("ip,t0 t1 ...", lda_post.py:35-59; an all-zero
+ * gamma row gets the script's twenty "0.0") and <dir>word_results.csv ("word,p0 p1 ...",
+ * word names joined with '_' and cut to 20 bytes like the script's S20 array,
+ * lda_post.py:70-122).  Numbers are printed the way Python-2 str() prints them: 12
+ * significant digits, ".0" appended to integral values.  `dir` is a prefix ("path/"). */
+int oni_lda_post_files(const char *dir, int32_t device);
+
 #ifdef __cplusplus
 }
 #endif

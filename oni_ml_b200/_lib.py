@@ -110,6 +110,7 @@ SIGNATURES = {
     "oni_score_get_stats": (C.c_int, [_vp, C.POINTER(_f64), C.POINTER(_f64), C.POINTER(_i64)]),
     "oni_score_flow_noalloc": (C.c_int, [_i32, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _f64, _i64,
                                          _vp, _vp, C.POINTER(_i64), _vp]),
+    "oni_lda_post_files": (C.c_int, [C.c_char_p, _i32]),
     "oni_lda_post": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, _i32, _vp, _vp]),
 }
 

@@ -218,14 +218,143 @@ int run_inf(int argc, char **argv)
     return rc;
 }
 
+// Python-2 str(float) / old-numpy str(float64): 12 significant digits, and ".0" appended when
+// the text would otherwise look like an integer (lda_post.py:50,119-121)
+int py2_float_str(char *out, double v)
+{
+    int n = snprintf(out, 48, "%.12g", v);
+    bool plain = true;
+    for (int i = 0; i < n; i++)
+        if (out[i] == '.' || out[i] == 'e' || out[i] == 'n' || out[i] == 'i') { plain = false; break; }
+    if (plain) { out[n++] = '.'; out[n++] = '0'; out[n] = 0; }
+    return n;
+}
+
+// whitespace-separated doubles of a text matrix; *cols from the first line
+int read_text_matrix(const char *path, std::vector<double> &a, int *rows, int *cols)
+{
+    FILE *f = fopen(path, "r");
+    if (!f) return oni_set_error(ONI_ERR_IO, "cannot open %s: %s", path, strerror(errno));
+    fseek(f, 0, SEEK_END);
+    const long len = ftell(f);
+    rewind(f);
+    std::string buf((size_t)(len > 0 ? len : 0), '\0');
+    const size_t got = fread(&buf[0], 1, buf.size(), f);
+    fclose(f);
+    buf.resize(got);
+    *rows = 0; *cols = 0;
+    const char *p = buf.c_str();
+    int c = 0;
+    while (*p) {
+        while (*p == ' ' || *p == '\t' || *p == '\r') p++;
+        if (*p == '\n') { if (c) { if (!*cols) *cols = c; else if (c != *cols) return oni_set_error(ONI_ERR_IO, "%s: ragged rows", path); (*rows)++; c = 0; } p++; continue; }
+        if (!*p) break;
+        char *e;
+        const double v = strtod(p, &e);
+        if (e == p) return oni_set_error(ONI_ERR_IO, "%s: not a number near byte %zu", path, (size_t)(p - buf.c_str()));
+        a.push_back(v); c++; p = e;
+    }
+    if (c) { if (!*cols) *cols = c; else if (c != *cols) return oni_set_error(ONI_ERR_IO, "%s: ragged rows", path); (*rows)++; }
+    return ONI_OK;
+}
+
+int read_lines(const char *path, std::vector<std::string> &lines)
+{
+    FILE *f = fopen(path, "r");
+    if (!f) return oni_set_error(ONI_ERR_IO, "cannot open %s: %s", path, strerror(errno));
+    char *line = nullptr; size_t cap = 0; ssize_t n;
+    while ((n = getline(&line, &cap, f)) >= 0) {
+        while (n > 0 && (line[n - 1] == '\n' || line[n - 1] == '\r')) n--;
+        lines.emplace_back(line, (size_t)n);
+    }
+    free(line);
+    fclose(f);
+    return ONI_OK;
+}
+
 }  // namespace
+
+// lda_post.py (ml_ops.sh:84): final.gamma / final.beta / doc.dat / words.dat under the prefix
+// `dir` -> doc_results.csv ("ip,t0 t1 ...") and word_results.csv ("word,p0 p1 ...").
+extern "C" int oni_lda_post_files(const char *dir, int32_t device)
+{
+    if (!dir) return oni_set_error(ONI_ERR_ARG, "lda_post_files: null directory prefix");
+    const std::string d(dir);
+    std::vector<double> gamma, beta;
+    int D = 0, K = 0, Kb = 0, V = 0;
+    ONI_TRY(read_text_matrix((d + "final.gamma").c_str(), gamma, &D, &K));
+    ONI_TRY(read_text_matrix((d + "final.beta").c_str(), beta, &Kb, &V));
+    if (K != Kb) return oni_set_error(ONI_ERR_IO, "final.gamma has %d topics, final.beta %d", K, Kb);
+    std::vector<std::string> docs, words;
+    ONI_TRY(read_lines((d + "doc.dat").c_str(), docs));
+    ONI_TRY(read_lines((d + "words.dat").c_str(), words));
+    if ((int)docs.size() < D) return oni_set_error(ONI_ERR_IO, "doc.dat has %zu lines, final.gamma %d rows", docs.size(), D);
+    if ((int)words.size() < V) return oni_set_error(ONI_ERR_IO, "words.dat has %zu lines, final.beta %d columns", words.size(), V);
+    std::vector<double> theta((size_t)D * K), pwz((size_t)V * K);
+    ONI_TRY(oni_lda_post(device, D, K, V, gamma.data(), beta.data(), 0, theta.data(), pwz.data()));
+
+    char num[64];
+    FILE *f = fopen((d + "doc_results.csv").c_str(), "w");
+    if (!f) return oni_set_error(ONI_ERR_IO, "cannot write %sdoc_results.csv: %s", dir, strerror(errno));
+    setvbuf(f, nullptr, _IOFBF, 1 << 20);
+    for (int i = 0; i < D; i++) {
+        // doc = linecache.getline(doc_file, j).split(',')[1]   (lda_post.py:56)
+        const std::string &ln = docs[i];
+        const size_t c1 = ln.find(',');
+        if (c1 == std::string::npos) { fclose(f); return oni_set_error(ONI_ERR_IO, "doc.dat line %d has no comma", i + 1); }
+        const size_t c2 = ln.find(',', c1 + 1);
+        fwrite(ln.data() + c1 + 1, 1, (c2 == std::string::npos ? ln.size() : c2) - c1 - 1, f);
+        fputc(',', f);
+        double total = 0;
+        for (int k = 0; k < K; k++) total = total + gamma[(size_t)i * K + k];
+        if (total > 0) {
+            for (int k = 0; k < K; k++) {
+                py2_float_str(num, theta[(size_t)i * K + k]);
+                if (k) fputc(' ', f);
+                fputs(num, f);
+            }
+        } else {
+            // the script's literal fallback: twenty "0.0", whatever K is (lda_post.py:54)
+            for (int k = 0; k < 20; k++) fputs(k ? " 0.0" : "0.0", f);
+        }
+        fputc('\n', f);
+    }
+    if (fclose(f) != 0) return oni_set_error(ONI_ERR_IO, "write failed on %sdoc_results.csv", dir);
+
+    f = fopen((d + "word_results.csv").c_str(), "w");
+    if (!f) return oni_set_error(ONI_ERR_IO, "cannot write %sword_results.csv: %s", dir, strerror(errno));
+    setvbuf(f, nullptr, _IOFBF, 1 << 20);
+    for (int w = 0; w < V; w++) {
+        // word = '_'.join(fields[1:]) cut to 20 bytes (the "S20" array, lda_post.py:78-83)
+        const std::string &ln = words[w];
+        const size_t c1 = ln.find(',');
+        std::string name = (c1 == std::string::npos) ? std::string() : ln.substr(c1 + 1);
+        for (char &ch : name) if (ch == ',') ch = '_';
+        if (name.size() > 20) name.resize(20);
+        fwrite(name.data(), 1, name.size(), f);
+        fputc(',', f);
+        for (int k = 0; k < K; k++) {
+            py2_float_str(num, pwz[(size_t)w * K + k]);
+            if (k) fputc(' ', f);
+            fputs(num, f);
+        }
+        fputc('\n', f);
+    }
+    if (fclose(f) != 0) return oni_set_error(ONI_ERR_IO, "write failed on %sword_results.csv", dir);
+    return ONI_OK;
+}
 
 extern "C" int oni_lda_main(int argc, char **argv)
 {
     if (argc > 1 && strcmp(argv[1], "est") == 0) return run_est(argc, argv);
     if (argc > 1 && strcmp(argv[1], "inf") == 0) return run_inf(argc, argv);
+    // two additions to the reference's command line: the Python stages either side of the engine
+    if (argc > 2 && strcmp(argv[1], "pre") == 0) return oni_lda_pre(argv[2]);            // lda_pre.py <dir>/
+    if (argc > 2 && strcmp(argv[1], "post") == 0) return oni_lda_post_files(argv[2], 0);  // lda_post.py <dir>/
     // lda-estimate.c:464-465
     printf("usage : lda est [alpha] [k] [settings] [#gpus] [data] [random/seeded/*] [output directory]\n");
     printf("        lda inf [settings] [model] [data] [output filename]\n");
+    printf("        lda pre [dir/]    (lda_pre.py: doc_wc.dat -> words.dat doc.dat model.dat)\n");
+    printf("        lda post [dir/]   (lda_post.py: final.gamma final.beta -> doc_results.csv word_results.csv)\n");
     return ONI_OK;
 }

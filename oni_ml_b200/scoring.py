@@ -113,3 +113,8 @@ def lda_post(gamma, logbeta, text_digits: int = 12, device: int = 0):
     theta = np.zeros((d, k)); pwz = np.zeros((v, k))
     check(L.oni_lda_post(device, d, k, v, ptr(gamma), ptr(logbeta), text_digits, ptr(theta), ptr(pwz)))
     return theta, pwz
+
+
+def lda_post_files(dir_prefix: str, device: int = 0) -> None:
+    """oni_lda_post_files: lda_post.py as a whole (doc_results.csv, word_results.csv)."""
+    check(_lib.load().oni_lda_post_files(dir_prefix.encode(), device))

@@ -131,3 +131,43 @@ def test_lda_post_tables_match_oracle(golden_dir):
     # 12-digit rounding; allow one unit of the 12th digit
     assert np.max(np.abs(pwz - pw) / pw) < 2e-12
     assert np.allclose(theta.sum(1), 1.0, atol=1e-10)
+
+
+def test_lda_post_files_csvs(golden_dir, tmp_path):
+    """oni_lda_post_files: doc_results.csv / word_results.csv in lda_post.py's shapes, values
+    equal to the oracle's 12-digit tables, names cut to 20 bytes, ".0" on integral values."""
+    import os
+    import shutil
+    from oni_ml_b200 import files
+    g = os.path.join(golden_dir, "c0_k20")
+    for n in ("final.gamma", "final.beta"):
+        shutil.copy(os.path.join(g, n), tmp_path / n)
+    gamma = files.read_matrix(os.path.join(g, "final.gamma"))
+    beta = files.read_matrix(os.path.join(g, "final.beta"))
+    D, V = gamma.shape[0], beta.shape[1]
+    with open(tmp_path / "doc.dat", "w") as f:
+        for i in range(D):
+            f.write("%d,10.0.%d.%d\n" % (i + 1, i // 256, i % 256))
+    with open(tmp_path / "words.dat", "w") as f:
+        for w in range(V):
+            f.write("%d,%s\n" % (w, "65535.0_9.0_9.0_9.0_tail" if w == 3 else "a,b" if w == 4 else "%d.0_1.0_2.0_3.0" % w))
+    # a zero gamma row exercises the script's literal fallback
+    lines = open(tmp_path / "final.gamma").read().splitlines()
+    lines[5] = " ".join(["0.0000000000"] * 20)
+    open(tmp_path / "final.gamma", "w").write("\n".join(lines) + "\n")
+    gamma[5] = 0.0
+    scoring.lda_post_files(str(tmp_path) + "/")
+    L = pyoracle.lib()
+    th = np.zeros_like(gamma); pw = np.zeros((V, 20))
+    L.orc_theta_from_gamma(D, 20, gamma, th)
+    L.orc_pwz_from_beta(20, V, beta, pw)
+    rows = open(tmp_path / "doc_results.csv").read().splitlines()
+    assert len(rows) == D and rows[0].startswith("10.0.0.0,") and rows[5] == "10.0.0.5," + " ".join(["0.0"] * 20)
+    got = np.array([[float(x) for x in r.split(",")[1].split(" ")] for r in rows])
+    assert np.array_equal(got, th)
+    wrows = open(tmp_path / "word_results.csv").read().splitlines()
+    assert len(wrows) == V
+    assert wrows[3].split(",")[0] == "65535.0_9.0_9.0_9.0_"[:20] and wrows[4].split(",")[0] == "a_b"
+    gotw = np.array([[float(x) for x in r.split(",")[1].split(" ")] for r in wrows])
+    assert np.max(np.abs(gotw - pw) / pw) < 2e-12
+    assert all(("." in t or "e" in t) for r in rows[:50] for t in r.split(",")[1].split(" "))
