@@ -369,6 +369,8 @@ double now_seconds()
 }  // namespace
 
 // ------------------------------------------------------------------- lifecycle
+static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_settings *st, oni_lda_ctx *c);
+
 extern "C" int oni_lda_create(int32_t device, int32_t K, int32_t V, const oni_lda_settings *st,
                               oni_lda_ctx **out)
 {
@@ -385,8 +387,18 @@ extern "C" int oni_lda_create(int32_t device, int32_t K, int32_t V, const oni_ld
         return oni_set_error(ONI_ERR_CUDA, "no CUDA device: this engine has no CPU path");
     if (device < 0 || device >= ndev)
         return oni_set_error(ONI_ERR_ARG, "device %d of %d", device, ndev);
-    ONI_CUDA(cudaSetDevice(device));
     oni_lda_ctx *c = new oni_lda_ctx();
+    c->G = G; c->T = T;
+    const int rc = create_impl(device, K, V, st, c);
+    if (rc != ONI_OK) { oni_lda_destroy(c); return rc; }  // nothing half-built survives a failure
+    *out = c;
+    return ONI_OK;
+}
+
+static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_settings *st, oni_lda_ctx *c)
+{
+    const int G = c->G, T = c->T;
+    ONI_CUDA(cudaSetDevice(device));
     c->device = device; c->K = K; c->KP = (K + 3) & ~3; c->V = V; c->G = G; c->T = T;
     c->st = *st; c->var_max_iter = st->var_max_iter;
     cudaDeviceProp prop;
@@ -418,7 +430,6 @@ extern "C" int oni_lda_create(int32_t device, int32_t K, int32_t V, const oni_ld
     ONI_CUDA(cudaMemset(c->d_nan, 0, sizeof(int32_t)));
     ONI_CUDA(cudaMemset(c->d_ss, 0, sizeof(double) * c->ss_count()));
     ONI_CUDA(cudaMallocHost((void **)&c->h_pinned, sizeof(double) * 8));
-    *out = c;
     return ONI_OK;
 }
 

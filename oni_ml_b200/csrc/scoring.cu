@@ -311,6 +311,8 @@ struct oni_score_ctx {
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
 };
 
+extern "C" void oni_score_destroy(oni_score_ctx *c);
+
 extern "C" int oni_score_create(int32_t device, int32_t K, int32_t D, int32_t V, const double *theta,
                                 const double *pwz, oni_score_ctx **out)
 {
@@ -321,20 +323,25 @@ extern "C" int oni_score_create(int32_t device, int32_t K, int32_t D, int32_t V,
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return oni_set_error(ONI_ERR_CUDA, "no CUDA device: this engine has no CPU path");
     if (device < 0 || device >= ndev) return oni_set_error(ONI_ERR_ARG, "device %d of %d", device, ndev);
-    ONI_CUDA(cudaSetDevice(device));
     oni_score_ctx *c = new oni_score_ctx();
     c->device = device; c->K = K; c->D = D; c->V = V;
-    cudaDeviceProp prop;
-    ONI_CUDA(cudaGetDeviceProperties(&prop, device));
-    c->sm_count = prop.multiProcessorCount;
-    ONI_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    ONI_CUDA(cudaEventCreate(&c->e0)); ONI_CUDA(cudaEventCreate(&c->e1)); ONI_CUDA(cudaEventCreate(&c->e2));
-    ONI_CUDA(cudaMalloc((void **)&c->d_theta, sizeof(double) * std::max<size_t>(1, (size_t)D * K)));
-    ONI_CUDA(cudaMalloc((void **)&c->d_pwz, sizeof(double) * std::max<size_t>(1, (size_t)V * K)));
-    ONI_CUDA(cudaMalloc((void **)&c->d_counter, sizeof(unsigned long long)));
-    ONI_CUDA(cudaMalloc((void **)&c->d_totals, sizeof(unsigned long long) * RS_MAX_PASSES * 256));
-    ONI_CUDA(cudaMemcpy(c->d_theta, theta, sizeof(double) * (size_t)D * K, cudaMemcpyHostToDevice));
-    ONI_CUDA(cudaMemcpy(c->d_pwz, pwz, sizeof(double) * (size_t)V * K, cudaMemcpyHostToDevice));
+    auto build = [&]() -> int {
+        ONI_CUDA(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        ONI_CUDA(cudaGetDeviceProperties(&prop, device));
+        c->sm_count = prop.multiProcessorCount;
+        ONI_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        ONI_CUDA(cudaEventCreate(&c->e0)); ONI_CUDA(cudaEventCreate(&c->e1)); ONI_CUDA(cudaEventCreate(&c->e2));
+        ONI_CUDA(cudaMalloc((void **)&c->d_theta, sizeof(double) * std::max<size_t>(1, (size_t)D * K)));
+        ONI_CUDA(cudaMalloc((void **)&c->d_pwz, sizeof(double) * std::max<size_t>(1, (size_t)V * K)));
+        ONI_CUDA(cudaMalloc((void **)&c->d_counter, sizeof(unsigned long long)));
+        ONI_CUDA(cudaMalloc((void **)&c->d_totals, sizeof(unsigned long long) * RS_MAX_PASSES * 256));
+        ONI_CUDA(cudaMemcpy(c->d_theta, theta, sizeof(double) * (size_t)D * K, cudaMemcpyHostToDevice));
+        ONI_CUDA(cudaMemcpy(c->d_pwz, pwz, sizeof(double) * (size_t)V * K, cudaMemcpyHostToDevice));
+        return ONI_OK;
+    };
+    const int rc = build();
+    if (rc != ONI_OK) { oni_score_destroy(c); return rc; }  // nothing half-built survives a failure
     *out = c;
     return ONI_OK;
 }

@@ -151,3 +151,23 @@ def test_lda_pre_byte_identical_to_reference_script(tmp_path, golden_dir):
     assert c.nnz == 1501 and c.num_docs == len(open(tmp_path / "doc.dat").readlines())
     with pytest.raises(_lib.OniError):
         lda.lda_pre(str(tmp_path / "nowhere") + "/")
+
+
+def test_product_never_touches_the_oracle():
+    """The oracle is test infrastructure: nothing under oni_ml_b200/ (Python or C/CUDA) may
+    import, include, link or execute anything under oracle/."""
+    pkg = os.path.join(ROOT, "oni_ml_b200")
+    offenders = []
+    for base, _dirs, names in os.walk(pkg):
+        if os.sep + "build" in base:
+            continue
+        for n in names:
+            if n.endswith((".py", ".c", ".cu", ".cuh", ".h", ".inc")) or n == "Makefile":
+                text = open(os.path.join(base, n), errors="replace").read()
+                if re.search(r"(from|import)\s+oracle|oracle/|pyoracle|liboni_oracle|lda_ref", text):
+                    offenders.append(os.path.join(base, n))
+    assert offenders == []
+    # and the shared library has no dependency on it
+    import subprocess
+    deps = subprocess.run(["ldd", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in deps and "torch" not in deps
