@@ -45,11 +45,15 @@ def test_initial_model_byte_identical(golden_dir, c0_corpus, tmp_path):
 
 
 @pytest.mark.parametrize("k,alpha,vmax", [(20, 2.5, 20), (5, 0.1, 5), (37, 1.0, -1), (8, 0.5, 20),
-                                          (50, 0.3, 20), (3, 2.0, 20), (64, 1.5, 10)])
+                                          (50, 0.3, 20), (3, 2.0, 20), (64, 1.5, 10), (1, 1.0, 5),
+                                          (2, 0.7, 20), (12, 0.9, 20), (100, 0.2, 8), (200, 0.05, 6),
+                                          (256, 1.0, 4), (20, 0.004, 20)])
 def test_single_e_step_matches_oracle(c0_corpus, k, alpha, vmax):
     """One E-step from the same model: gamma, per-document bound, and the M-step's
     beta (i.e. the reduced class_word / class_total) against the oracle."""
-    st = _lib.Settings(vmax, 1e-6, 20, 1e-6, 1)
+    # (with one topic the reference's alpha Newton is 0/0 -- its alpha_suffstats is exactly 0 --
+    #  so that case runs with "alpha fixed")
+    st = _lib.Settings(vmax, 1e-6, 20, 1e-6, 0 if k == 1 else 1)
     with lda.LdaEngine(0, k, c0_corpus.num_terms, st) as eng:
         eng.set_corpus(c0_corpus)
         eng.init_random(1234, alpha)
@@ -69,7 +73,10 @@ def test_single_e_step_matches_oracle(c0_corpus, k, alpha, vmax):
     L.orc_mle_beta(k, c0_corpus.num_terms, ref["class_word"], ref["class_total"], want)
     assert np.array_equal(lb1 == -100.0, want == -100.0)
     assert rel_err(lb1, want) < 1e-9
-    assert abs(a1 - L.orc_opt_alpha(ref["alpha_ss"], ref["num_docs"], k)) / a1 < 1e-9
+    if k > 1:
+        assert abs(a1 - L.orc_opt_alpha(ref["alpha_ss"], ref["num_docs"], k)) / a1 < 1e-9
+    else:
+        assert a1 == alpha
     assert stats["word_visits"] == ref["word_visits"]
 
 
