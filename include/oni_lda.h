@@ -324,6 +324,54 @@ int oni_lda_post(int32_t device, int32_t num_docs, int32_t num_topics, int32_t n
  * significant digits, ".0" appended to integral values.  `dir` is a prefix ("path/"). */
 int oni_lda_post_files(const char *dir, int32_t device);
 
+/* ---- raw events -> scored rows: the Spark scripts around the score loop ------------------
+ *
+ * Replaces flow_post_lda.scala:48-248 and dns_post_lda.scala:55-330 as a whole (SURVEY.md
+ * 8(f) N3).  `open` does the host work on all cores: header removal and the field-count
+ * filter (flow :128-135, dns :138), the empirical-CDF cut vectors (flow :67-103,148-158; dns
+ * :214-266), binning (flow :161-180, dns :201-204), the port -> word rule with the script's
+ * own column naming (flow :182-218), the sub-domain, entropy and top-domain features (dns
+ * :154-190,206-212,272), and the lookups of IPs and words in doc_results.csv /
+ * word_results.csv (a miss becomes index -1 = the script's constant vector).
+ * `score_write` runs the score loop, threshold and ranking on the GPU (oni_score_flow /
+ * oni_score_dns) and writes the surviving rows, original fields first, then the derived
+ * columns, then the score(s), comma separated, one file instead of Spark's part-* directory.
+ *
+ * Inputs: flow = the nfdump CSV the script reads (27 columns, first line = header);
+ * dns = one line per event holding the eight columns the script selects from its parquet
+ * files, comma separated (frame_time, unix_tstamp, frame_len, ip_dst, dns_qry_name,
+ * dns_qry_class, dns_qry_type, dns_qry_rcode), plus the Alexa-style "rank,domain" list the
+ * script opens as top-1m.csv.
+ *
+ * Fixed here because the reference leaves them to the JVM: numbers are printed as the
+ * shortest decimal that reads back to the same double, in Double.toString's layout; rows of
+ * equal score keep their input order; the entropy sum runs over the distinct bytes in
+ * ascending order.  A field that does not parse as a number is an error (the script dies
+ * with a NumberFormatException). */
+typedef struct oni_events oni_events;
+int oni_flow_events_open(const char *flow_csv, const char *doc_results_csv,
+                         const char *word_results_csv, oni_events **out);
+int oni_dns_events_open(const char *dns_csv, const char *top_domains_csv,
+                        const char *doc_results_csv, const char *word_results_csv,
+                        oni_events **out);
+void oni_events_close(oni_events *ev);
+/* lines read, rows kept by the filters, distinct keys of the two result tables */
+int oni_events_info(const oni_events *ev, int64_t *lines_in, int64_t *rows, int32_t *num_docs,
+                    int32_t *num_words);
+/* cut vector `which`: flow 0 time, 1 ibyt, 2 ipkt; dns 0 unix_tstamp, 1 frame_len,
+ * 2 subdomain.length, 3 subdomain.entropy, 4 num.periods.  *n = 10 or 5. */
+int oni_events_cuts(const oni_events *ev, int32_t which, double *out, int32_t cap, int32_t *n);
+/* the indices handed to the scorer, [rows] each: flow (src_doc, dst_doc, src_word, dst_word);
+ * dns (doc, -, word, -).  Any pointer may be NULL. */
+int oni_events_indices(const oni_events *ev, int32_t *a_doc, int32_t *b_doc, int32_t *a_word,
+                       int32_t *b_word);
+/* text of kept row `row` as the script holds it just before scoring (no score columns).
+ * Returns its length (the copy is cut to cap-1 bytes and NUL terminated), -1 on a bad row. */
+int64_t oni_events_row_text(const oni_events *ev, int64_t row, char *buf, int64_t cap);
+/* GPU: score every kept row, keep score < tol, rank ascending, write the rows to out_path */
+int oni_events_score_write(oni_events *ev, double tol, const char *out_path, int32_t device,
+                           int64_t *num_scored);
+
 #ifdef __cplusplus
 }
 #endif

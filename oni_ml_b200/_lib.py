@@ -111,6 +111,14 @@ SIGNATURES = {
     "oni_score_flow_noalloc": (C.c_int, [_i32, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _f64, _i64,
                                          _vp, _vp, C.POINTER(_i64), _vp]),
     "oni_lda_post_files": (C.c_int, [C.c_char_p, _i32]),
+    "oni_flow_events_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(_vp)]),
+    "oni_dns_events_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(_vp)]),
+    "oni_events_close": (None, [_vp]),
+    "oni_events_info": (C.c_int, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i32), C.POINTER(_i32)]),
+    "oni_events_cuts": (C.c_int, [_vp, _i32, _vp, _i32, C.POINTER(_i32)]),
+    "oni_events_indices": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
+    "oni_events_row_text": (_i64, [_vp, _i64, C.c_char_p, _i64]),
+    "oni_events_score_write": (C.c_int, [_vp, _f64, C.c_char_p, _i32, C.POINTER(_i64)]),
     "oni_lda_post": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, _i32, _vp, _vp]),
 }
 

@@ -344,6 +344,26 @@ extern "C" int oni_lda_post_files(const char *dir, int32_t device)
     return ONI_OK;
 }
 
+// <type>_post_lda.scala: HPATH holds doc_results.csv and word_results.csv; TOL is parsed like toDouble
+static int run_events(int flow, const char *events, const char *top, const char *hpath, const char *tol,
+                      const char *out_path)
+{
+    char *end = nullptr;
+    const double t = strtod(tol, &end);
+    if (end == tol || *end) return oni_set_error(ONI_ERR_ARG, "threshold '%s' is not a number", tol);
+    const std::string h(hpath);
+    const std::string docs = h + "doc_results.csv", words = h + "word_results.csv";
+    oni_events *ev = nullptr;
+    ONI_TRY(flow ? oni_flow_events_open(events, docs.c_str(), words.c_str(), &ev)
+                 : oni_dns_events_open(events, top, docs.c_str(), words.c_str(), &ev));
+    int64_t rows = 0, scored = 0;
+    oni_events_info(ev, nullptr, &rows, nullptr, nullptr);
+    const int rc = oni_events_score_write(ev, t, out_path, 0, &scored);
+    oni_events_close(ev);
+    if (rc == ONI_OK) printf("%lld of %lld events below %s -> %s\n", (long long)scored, (long long)rows, tol, out_path);
+    return rc;
+}
+
 extern "C" int oni_lda_main(int argc, char **argv)
 {
     if (argc > 1 && strcmp(argv[1], "est") == 0) return run_est(argc, argv);
@@ -351,10 +371,15 @@ extern "C" int oni_lda_main(int argc, char **argv)
     // two additions to the reference's command line: the Python stages either side of the engine
     if (argc > 2 && strcmp(argv[1], "pre") == 0) return oni_lda_pre(argv[2]);            // lda_pre.py <dir>/
     if (argc > 2 && strcmp(argv[1], "post") == 0) return oni_lda_post_files(argv[2], 0);  // lda_post.py <dir>/
+    // the Spark scoring stage (ml_ops.sh:108): <type>_post_lda.scala with FLOW_PATH / DNS_PATH, HPATH and TOL
+    if (argc > 5 && strcmp(argv[1], "flow_post") == 0) return run_events(1, argv[2], nullptr, argv[3], argv[4], argv[5]);
+    if (argc > 6 && strcmp(argv[1], "dns_post") == 0) return run_events(0, argv[2], argv[3], argv[4], argv[5], argv[6]);
     // lda-estimate.c:464-465
     printf("usage : lda est [alpha] [k] [settings] [#gpus] [data] [random/seeded/*] [output directory]\n");
     printf("        lda inf [settings] [model] [data] [output filename]\n");
     printf("        lda pre [dir/]    (lda_pre.py: doc_wc.dat -> words.dat doc.dat model.dat)\n");
     printf("        lda post [dir/]   (lda_post.py: final.gamma final.beta -> doc_results.csv word_results.csv)\n");
+    printf("        lda flow_post [flow.csv] [hpath/] [tol] [scored file]              (flow_post_lda.scala)\n");
+    printf("        lda dns_post [dns.csv] [top-1m.csv] [hpath/] [tol] [scored file]   (dns_post_lda.scala)\n");
     return ONI_OK;
 }

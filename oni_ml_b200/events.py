@@ -1,0 +1,96 @@
+"""Python face of the event pipelines around the scorer (flow_post_lda.scala,
+dns_post_lda.scala): raw rows -> features -> indices -> scored rows.  Forwards
+to liboni_lda.so (csrc/events.cu); no featurisation or arithmetic happens here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check, ptr
+
+
+class _Events:
+    _CUTS: tuple = ()
+
+    def __init__(self):
+        self._L = _lib.load()
+        self._h = C.c_void_p()
+
+    def close(self):
+        if self._h:
+            self._L.oni_events_close(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def info(self) -> dict:
+        a, b, d, w = C.c_int64(), C.c_int64(), C.c_int32(), C.c_int32()
+        check(self._L.oni_events_info(self._h, C.byref(a), C.byref(b), C.byref(d), C.byref(w)))
+        return dict(lines_in=a.value, rows=b.value, num_docs=d.value, num_words=w.value)
+
+    def cuts(self) -> dict:
+        out = {}
+        for which, name in enumerate(self._CUTS):
+            buf = np.zeros(10)
+            n = C.c_int32()
+            check(self._L.oni_events_cuts(self._h, which, ptr(buf), 10, C.byref(n)))
+            out[name] = buf[: n.value].copy()
+        return out
+
+    def row_text(self, row: int) -> str:
+        n = self._L.oni_events_row_text(self._h, row, None, 0)
+        if n < 0:
+            check(1)
+        buf = C.create_string_buffer(n + 1)
+        self._L.oni_events_row_text(self._h, row, buf, n + 1)
+        return buf.value.decode("utf-8", "replace")
+
+    def score_write(self, tol: float, out_path: str, device: int = 0) -> int:
+        n = C.c_int64()
+        check(self._L.oni_events_score_write(self._h, float(tol), out_path.encode(), device, C.byref(n)))
+        return n.value
+
+
+class FlowEvents(_Events):
+    """oni_flow_events_open: flow_post_lda.scala up to the score loop."""
+    _CUTS = ("time", "ibyt", "ipkt")
+
+    def __init__(self, flow_csv: str, doc_results_csv: str, word_results_csv: str):
+        super().__init__()
+        check(self._L.oni_flow_events_open(flow_csv.encode(), doc_results_csv.encode(),
+                                           word_results_csv.encode(), C.byref(self._h)))
+
+    def indices(self):
+        n = self.info()["rows"]
+        a = [np.zeros(max(n, 1), dtype=np.int32) for _ in range(4)]
+        check(self._L.oni_events_indices(self._h, *(ptr(x) for x in a)))
+        return tuple(x[:n] for x in a)  # src_doc, dst_doc, src_word, dst_word
+
+
+class DnsEvents(_Events):
+    """oni_dns_events_open: dns_post_lda.scala up to the score loop."""
+    _CUTS = ("unix_tstamp", "frame_len", "subdomain_length", "subdomain_entropy", "num_periods")
+
+    def __init__(self, dns_csv: str, top_domains_csv: str, doc_results_csv: str, word_results_csv: str):
+        super().__init__()
+        check(self._L.oni_dns_events_open(dns_csv.encode(), top_domains_csv.encode(), doc_results_csv.encode(),
+                                          word_results_csv.encode(), C.byref(self._h)))
+
+    def indices(self):
+        n = self.info()["rows"]
+        d, w = np.zeros(max(n, 1), dtype=np.int32), np.zeros(max(n, 1), dtype=np.int32)
+        check(self._L.oni_events_indices(self._h, ptr(d), None, ptr(w), None))
+        return d[:n], w[:n]

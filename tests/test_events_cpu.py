@@ -1,0 +1,174 @@
+"""Featurisation of raw events (csrc/events.cu) against the Python restatement of the Spark
+scripts (oracle/events_oracle.py).  Host work only: runs without a GPU."""
+import ctypes as C
+import os
+import random
+import struct
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import events_data  # noqa: E402
+import events_oracle as eo  # noqa: E402
+
+from oni_ml_b200 import _lib  # noqa: E402
+from oni_ml_b200.events import DnsEvents, FlowEvents  # noqa: E402
+
+
+def test_double_to_string_matches_the_restatement():
+    L = _lib.load()
+    fn = L.oni_internal_java_double_str
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_double, C.c_char_p]
+    buf = C.create_string_buffer(64)
+    rnd = random.Random(3)
+    vals = [0.0, -0.0, 1.0, 80.0, 111111.0, 333333.0, 65535.0, 0.05, 0.1, 1e-3, 9.999e-4, 1e7, 9999999.0, 1.5e-20,
+            0.018333333333333333, 23.999722222222225, 1e21, 1e22, 1e23, 5e-324, 1.7976931348623157e308, 2.0 ** -44,
+            float("inf"), float("-inf"), float("nan"), 123456789012345680.0, 4.35, 0.3, 2.675, 100.0, 1234.5]
+    vals += [rnd.random() for _ in range(2000)]
+    vals += [rnd.random() * 10 ** rnd.randint(-30, 30) for _ in range(2000)]
+    vals += [struct.unpack("<d", struct.pack("<Q", rnd.getrandbits(63)))[0] for _ in range(2000)]
+    for v in vals:
+        n = fn(v, buf)
+        got = buf.value.decode()
+        assert n == len(got)
+        assert got == eo.jdouble(v), repr(v)
+    # spot values of Double.toString known from the JDK documentation's rules
+    assert eo.jdouble(80.0) == "80.0" and eo.jdouble(1e7) == "1.0E7" and eo.jdouble(1e-3) == "0.001"
+    assert eo.jdouble(9.999e-4) == "9.999E-4" and eo.jdouble(0.05) == "0.05"
+
+
+def _flow_case(tmp_path, n, seed):
+    flow, docs, words = events_data.make_flow(str(tmp_path), n=n, seed=seed)
+    text = open(flow).read()
+    first = eo.flow_post(text, open(docs).read(), "", 1.0)
+    vocab = []
+    for r in first["rows"]:
+        f = r.split(",")
+        vocab += [f[33], f[34]]
+    events_data.write_word_results(words, vocab)
+    return flow, docs, words
+
+
+def test_flow_featurisation(tmp_path):
+    flow, docs, words = _flow_case(tmp_path, 4000, 7)
+    ref = eo.flow_post(open(flow).read(), open(docs).read(), open(words).read(), 1.0)
+    with FlowEvents(flow, docs, words) as ev:
+        info = ev.info()
+        assert info["rows"] == len(ref["rows"]) and info["rows"] > 3500
+        assert info["lines_in"] == len(eo.text_lines(open(flow).read()))
+        cuts = ev.cuts()
+        for name in ("time", "ibyt", "ipkt"):
+            assert cuts[name].tolist() == ref["cuts"][name], name
+        for i in range(info["rows"]):
+            assert ev.row_text(i) == ref["rows"][i], i
+        # indices: first-appearance row of the key in the result files, -1 on a miss
+        tdocs = {}
+        for ln in eo.text_lines(open(docs).read()):
+            tdocs.setdefault(ln.split(",")[0], len(tdocs))
+        twords = {}
+        for ln in eo.text_lines(open(words).read()):
+            twords.setdefault(ln.split(",")[0], len(twords))
+        sd, dd, sw, dw = ev.indices()
+        hits = 0
+        for i, r in enumerate(ref["rows"]):
+            f = r.split(",")
+            assert sd[i] == tdocs.get(f[8], -1) and dd[i] == tdocs.get(f[9], -1)
+            assert sw[i] == twords.get(f[33], -1) and dw[i] == twords.get(f[34], -1)
+            hits += (sw[i] >= 0) + (dw[i] >= 0)
+        assert 0 < hits < 2 * len(ref["rows"])  # both hits and misses (20-byte names, dropped words) occur
+        assert info["num_docs"] == len(tdocs) and info["num_words"] == len(twords)
+
+
+def test_flow_tiny_and_degenerate_inputs(tmp_path):
+    docs = tmp_path / "d.csv"
+    words = tmp_path / "w.csv"
+    docs.write_text("1.1.1.1," + " ".join(["0.05"] * 20) + "\n")
+    words.write_text("80.0_0.0_0.0_0.0," + " ".join(["0.05"] * 20) + "\n")
+    # header only / empty file: no rows, all cuts zero
+    for body in ("", events_data.FLOW_HEADER + "\n"):
+        p = tmp_path / "f.csv"
+        p.write_text(body)
+        with FlowEvents(str(p), str(docs), str(words)) as ev:
+            assert ev.info()["rows"] == 0
+            assert all((v == 0).all() for v in ev.cuts().values())
+    # one row: its own values sit at ecdf 1.0, above every quantile -> cuts stay 0, bins count cuts below the value
+    rnd = random.Random(1)
+    row = events_data.flow_row(rnd, ["1.1.1.1", "2.2.2.2"])
+    p = tmp_path / "one.csv"
+    p.write_text(events_data.FLOW_HEADER + "\n" + ",".join(row) + "\n")
+    ref = eo.flow_post(p.read_text(), docs.read_text(), words.read_text(), 1.0)
+    with FlowEvents(str(p), str(docs), str(words)) as ev:
+        assert ev.info()["rows"] == 1 and ev.row_text(0) == ref["rows"][0]
+    # a field that is not a number: the script dies, the library reports it
+    bad = list(row)
+    bad[16] = "many"
+    p.write_text(events_data.FLOW_HEADER + "\n" + ",".join(bad) + "\n")
+    with pytest.raises(_lib.OniError):
+        FlowEvents(str(p), str(docs), str(words))
+    with pytest.raises(_lib.OniError):
+        FlowEvents(str(tmp_path / "missing.csv"), str(docs), str(words))
+    # a result table with fewer than 20 numbers per line cannot feed the 0..19 loop
+    words.write_text("w,0.5 0.5\n")
+    p.write_text(events_data.FLOW_HEADER + "\n" + ",".join(row) + "\n")
+    with pytest.raises(_lib.OniError):
+        FlowEvents(str(p), str(docs), str(words))
+
+
+def _dns_case(tmp_path, n, seed):
+    dns, top, docs, words = events_data.make_dns(str(tmp_path), n=n, seed=seed)
+    first = eo.dns_post(open(dns).read(), open(top).read(), open(docs).read(), "", 1.0)
+    events_data.write_word_results(words, [r.split(",")[14] for r in first["rows"]], cut20=False)
+    return dns, top, docs, words
+
+
+def test_dns_featurisation(tmp_path):
+    dns, top, docs, words = _dns_case(tmp_path, 4000, 13)
+    ref = eo.dns_post(open(dns).read(), open(top).read(), open(docs).read(), open(words).read(), 1.0)
+    with DnsEvents(dns, top, docs, words) as ev:
+        info = ev.info()
+        assert info["rows"] == len(ref["rows"]) and info["rows"] > 3800
+        cuts = ev.cuts()
+        for name, want in ref["cuts"].items():
+            assert cuts[name].tolist() == want, name
+        for i in range(info["rows"]):
+            assert ev.row_text(i) == ref["rows"][i], i
+        tdocs, twords = {}, {}
+        for ln in eo.text_lines(open(docs).read()):
+            tdocs.setdefault(ln.split(",")[0], len(tdocs))
+        for ln in eo.text_lines(open(words).read()):
+            twords.setdefault(ln.split(",")[0], len(twords))
+        d, w = ev.indices()
+        for i, r in enumerate(ref["rows"]):
+            f = r.split(",")
+            assert d[i] == tdocs.get(f[3], -1) and w[i] == twords.get(f[14], -1)
+        assert (w >= 0).any() and (w < 0).any() and (d >= 0).any() and (d < 0).any()
+
+
+def test_cuts_with_many_threads_match_one_thread(tmp_path, monkeypatch):
+    """The sorted-slices-then-merge path (above 2^20 samples) gives the same cut vectors."""
+    rnd = random.Random(5)
+    ips = ["1.1.1.%d" % i for i in range(8)]
+    docs = tmp_path / "d.csv"
+    words = tmp_path / "w.csv"
+    docs.write_text("1.1.1.1," + " ".join(["0.05"] * 20) + "\n")
+    words.write_text("w," + " ".join(["0.05"] * 20) + "\n")
+    base = [",".join(events_data.flow_row(rnd, ips)) for _ in range(4096)]
+    p = tmp_path / "big.csv"
+    with open(p, "w") as fh:
+        fh.write(events_data.FLOW_HEADER + "\n")
+        for rep in range(300):
+            fh.write("\n".join(base) + "\n")
+    out = []
+    for threads in ("1", "7"):
+        monkeypatch.setenv("ONI_IO_THREADS", threads)
+        with FlowEvents(str(p), str(docs), str(words)) as ev:
+            assert ev.info()["rows"] == 4096 * 300
+            out.append({k: v.tolist() for k, v in ev.cuts().items()})
+    assert out[0] == out[1]
+    ref = eo.flow_post(events_data.FLOW_HEADER + "\n" + "\n".join(base) + "\n", docs.read_text(), words.read_text(), 0.0)
+    assert out[0] == ref["cuts"]  # repeating the sample leaves its empirical CDF unchanged
