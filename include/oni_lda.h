@@ -368,6 +368,13 @@ int oni_events_indices(const oni_events *ev, int32_t *a_doc, int32_t *b_doc, int
 /* text of kept row `row` as the script holds it just before scoring (no score columns).
  * Returns its length (the copy is cut to cap-1 bytes and NUL terminated), -1 on a bad row. */
 int64_t oni_events_row_text(const oni_events *ev, int64_t row, char *buf, int64_t cap);
+/* The pre-LDA stage (flow_pre_lda.scala:371-382, dns_pre_lda.scala:326-330): one line
+ * "ip,word,count" per distinct (ip, word) -- the doc_wc.dat that lda_pre.py / oni_lda_pre read.
+ * Flow writes the source-side list, then the destination-side list (a pair can occur in both,
+ * as in the script).  Line order (Spark: hash partitioner) is first appearance here.  For this
+ * stage the handle may be opened with doc_results_csv = word_results_csv = NULL.  The scripts'
+ * optional analyst-feedback rows are not read: append them to the input file. */
+int oni_events_word_counts(const oni_events *ev, const char *out_path, int64_t *num_lines);
 /* GPU: score every kept row, keep score < tol, rank ascending, write the rows to out_path */
 int oni_events_score_write(oni_events *ev, double tol, const char *out_path, int32_t device,
                            int64_t *num_scored);

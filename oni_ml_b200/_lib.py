@@ -118,6 +118,7 @@ SIGNATURES = {
     "oni_events_cuts": (C.c_int, [_vp, _i32, _vp, _i32, C.POINTER(_i32)]),
     "oni_events_indices": (C.c_int, [_vp, _vp, _vp, _vp, _vp]),
     "oni_events_row_text": (_i64, [_vp, _i64, C.c_char_p, _i64]),
+    "oni_events_word_counts": (C.c_int, [_vp, C.c_char_p, C.POINTER(_i64)]),
     "oni_events_score_write": (C.c_int, [_vp, _f64, C.c_char_p, _i32, C.POINTER(_i64)]),
     "oni_lda_post": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, _i32, _vp, _vp]),
 }

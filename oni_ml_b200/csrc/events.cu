@@ -332,6 +332,7 @@ const char *const COUNTRY_CODES[] = {
 // ------------------------------------------------------------------ the handle
 struct oni_events {
     int kind = 0;  // 1 flow, 0 dns
+    bool has_tables = false;
     std::string data, top_text;
     Table docs, words;
     int64_t lines_in = 0;
@@ -654,7 +655,7 @@ void dns_row_text(const oni_events &ev, size_t i, std::string &out)
 int open_common(int kind, const char *events_csv, const char *top_csv, const char *doc_results,
                 const char *word_results, oni_events **out)
 {
-    if (!events_csv || !doc_results || !word_results || !out || (kind == 0 && !top_csv))
+    if (!events_csv || !out || (kind == 0 && !top_csv) || (!doc_results) != (!word_results))
         return oni_set_error(ONI_ERR_ARG, "events_open: null argument");
     *out = nullptr;
     oni_events *ev = new (std::nothrow) oni_events();
@@ -664,8 +665,9 @@ int open_common(int kind, const char *events_csv, const char *top_csv, const cha
     try {
         rc = slurp(events_csv, ev->data);
         if (rc == ONI_OK && kind == 0) rc = slurp(top_csv, ev->top_text);
-        if (rc == ONI_OK) rc = load_table(doc_results, ev->docs);
-        if (rc == ONI_OK) rc = load_table(word_results, ev->words);
+        ev->has_tables = doc_results != nullptr;  // absent for the pre-LDA word count
+        if (rc == ONI_OK && ev->has_tables) rc = load_table(doc_results, ev->docs);
+        if (rc == ONI_OK && ev->has_tables) rc = load_table(word_results, ev->words);
         if (rc == ONI_OK) rc = kind ? flow_open(*ev) : dns_open(*ev);
     } catch (const std::bad_alloc &) {
         rc = oni_set_error(ONI_ERR_NOMEM, "events_open: out of memory");
@@ -748,6 +750,8 @@ extern "C" int oni_events_score_write(oni_events *ev, double tol, const char *ou
                                       int64_t *num_scored)
 {
     if (!ev || !out_path) return oni_set_error(ONI_ERR_ARG, "events_score_write: null argument");
+    if (!ev->has_tables)
+        return oni_set_error(ONI_ERR_ARG, "events_score_write: opened without doc_results.csv / word_results.csv");
     const int64_t n = (int64_t)ev->row.size();
     std::vector<int64_t> idx((size_t)std::max<int64_t>(n, 1));
     std::vector<double> key(idx.size()), sa(idx.size()), sb(idx.size());
@@ -780,6 +784,54 @@ extern "C" int oni_events_score_write(oni_events *ev, double tol, const char *ou
     }
     if (fclose(f) != 0) return oni_set_error(ONI_ERR_IO, "write failed on %s", out_path);
     if (num_scored) *num_scored = total;
+    return ONI_OK;
+}
+
+// The word-count tail of flow_pre_lda.scala:371-382 and dns_pre_lda.scala:326-330: one line
+// "ip,word,count" per distinct (ip, word).  Flow counts the source side (row(8), src_word) and the
+// destination side (row(9), dest_word) separately and writes both lists, so a pair can appear
+// twice (lda_pre.py keeps both).  Spark leaves the line order to its hash partitioner; here:
+// first appearance, source-side list first.
+extern "C" int oni_events_word_counts(const oni_events *ev, const char *out_path, int64_t *num_lines)
+{
+    if (!ev || !out_path) return oni_set_error(ONI_ERR_ARG, "events_word_counts: null argument");
+    FILE *f = fopen(out_path, "w");
+    if (!f) return oni_set_error(ONI_ERR_IO, "cannot write %s: %s", out_path, strerror(errno));
+    setvbuf(f, nullptr, _IOFBF, 1 << 20);
+    const size_t n = ev->row.size();
+    int64_t lines = 0;
+    std::vector<sv> fld;
+    char w[256];
+    for (int side = 0; side < (ev->kind ? 2 : 1); side++) {
+        std::unordered_map<std::string, size_t> slot;
+        std::vector<std::pair<std::string, int64_t>> order;
+        std::string key;
+        for (size_t i = 0; i < n; i++) {
+            split_java(ev->row[i], ',', fld);
+            if (ev->kind) {
+                key.assign(fld[8 + side]);
+                key += ',';
+                if (ev->flags[i] & (side ? 4 : 2)) key += "-1_";
+                flow_word(*ev, i, w);
+            } else {
+                key.assign(fld[C_IPDST]);
+                key += ',';
+                dns_word(*ev, i, fld, w);
+            }
+            key += w;
+            auto it = slot.find(key);
+            if (it == slot.end()) {
+                slot.emplace(key, order.size());
+                order.emplace_back(key, 1);
+            } else {
+                order[it->second].second++;
+            }
+        }
+        for (auto &kv : order) fprintf(f, "%s,%lld\n", kv.first.c_str(), (long long)kv.second);
+        lines += (int64_t)order.size();
+    }
+    if (fclose(f) != 0) return oni_set_error(ONI_ERR_IO, "write failed on %s", out_path);
+    if (num_lines) *num_lines = lines;
     return ONI_OK;
 }
 

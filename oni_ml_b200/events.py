@@ -12,6 +12,10 @@ from . import _lib
 from ._lib import check, ptr
 
 
+def _enc(path):
+    return None if path is None else path.encode()
+
+
 class _Events:
     _CUTS: tuple = ()
 
@@ -58,6 +62,11 @@ class _Events:
         self._L.oni_events_row_text(self._h, row, buf, n + 1)
         return buf.value.decode("utf-8", "replace")
 
+    def word_counts(self, out_path: str) -> int:
+        n = C.c_int64()
+        check(self._L.oni_events_word_counts(self._h, out_path.encode(), C.byref(n)))
+        return n.value
+
     def score_write(self, tol: float, out_path: str, device: int = 0) -> int:
         n = C.c_int64()
         check(self._L.oni_events_score_write(self._h, float(tol), out_path.encode(), device, C.byref(n)))
@@ -68,10 +77,10 @@ class FlowEvents(_Events):
     """oni_flow_events_open: flow_post_lda.scala up to the score loop."""
     _CUTS = ("time", "ibyt", "ipkt")
 
-    def __init__(self, flow_csv: str, doc_results_csv: str, word_results_csv: str):
+    def __init__(self, flow_csv: str, doc_results_csv: str | None = None, word_results_csv: str | None = None):
         super().__init__()
-        check(self._L.oni_flow_events_open(flow_csv.encode(), doc_results_csv.encode(),
-                                           word_results_csv.encode(), C.byref(self._h)))
+        check(self._L.oni_flow_events_open(flow_csv.encode(), _enc(doc_results_csv), _enc(word_results_csv),
+                                           C.byref(self._h)))
 
     def indices(self):
         n = self.info()["rows"]
@@ -84,10 +93,11 @@ class DnsEvents(_Events):
     """oni_dns_events_open: dns_post_lda.scala up to the score loop."""
     _CUTS = ("unix_tstamp", "frame_len", "subdomain_length", "subdomain_entropy", "num_periods")
 
-    def __init__(self, dns_csv: str, top_domains_csv: str, doc_results_csv: str, word_results_csv: str):
+    def __init__(self, dns_csv: str, top_domains_csv: str, doc_results_csv: str | None = None,
+                 word_results_csv: str | None = None):
         super().__init__()
-        check(self._L.oni_dns_events_open(dns_csv.encode(), top_domains_csv.encode(), doc_results_csv.encode(),
-                                          word_results_csv.encode(), C.byref(self._h)))
+        check(self._L.oni_dns_events_open(dns_csv.encode(), top_domains_csv.encode(), _enc(doc_results_csv),
+                                          _enc(word_results_csv), C.byref(self._h)))
 
     def indices(self):
         n = self.info()["rows"]

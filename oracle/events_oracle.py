@@ -279,3 +279,30 @@ def dns_post(dns_text, top_text, doc_results_text, word_results_text, tol):
     return dict(cuts=dict(unix_tstamp=time_cuts, frame_len=frame_cuts, subdomain_length=sub_cuts,
                           subdomain_entropy=ent_cuts, num_periods=per_cuts),
                 rows=feat, scored=[e[2] for e in scored])
+
+
+# ---------------------------------------------------------------- the pre-LDA word counts
+def flow_word_counts(flow_text):
+    """flow_pre_lda.scala:371-382 (same featurisation as the post script, :268-366): "ip,word,count"
+    lines, source side then destination side; line order (unspecified in Spark) = first appearance."""
+    rows = flow_post(flow_text, "", "", 0.0)["rows"]
+    out = []
+    for a, b in ((8, 33), (9, 34)):
+        counts = {}
+        for r in rows:
+            f = r.split(",")
+            key = f[a] + " " + f[b]
+            counts[key] = counts.get(key, 0) + 1
+        out += [k.split(" ")[0] + "," + k.split(" ")[1] + "," + str(c) for k, c in counts.items()]
+    return out
+
+
+def dns_word_counts(dns_text, top_text):
+    """dns_pre_lda.scala:326 (featurisation :153-323 as in the post script)."""
+    rows = dns_post(dns_text, top_text, "", "", 0.0)["rows"]
+    counts = {}
+    for r in rows:
+        f = r.split(",")
+        key = f[3] + " " + f[14]
+        counts[key] = counts.get(key, 0) + 1
+    return [k.split(" ")[0] + "," + k.split(" ")[1] + "," + str(c) for k, c in counts.items()]

@@ -172,3 +172,28 @@ def test_cuts_with_many_threads_match_one_thread(tmp_path, monkeypatch):
     assert out[0] == out[1]
     ref = eo.flow_post(events_data.FLOW_HEADER + "\n" + "\n".join(base) + "\n", docs.read_text(), words.read_text(), 0.0)
     assert out[0] == ref["cuts"]  # repeating the sample leaves its empirical CDF unchanged
+
+
+def test_word_counts_feed_lda_pre(tmp_path):
+    """<type>_pre_lda.scala's doc_wc.dat, then oni_lda_pre on it: the chain ml_ops.sh:44-67 runs."""
+    import subprocess
+    from oni_ml_b200 import LDA_BIN
+    from oni_ml_b200.lda import lda_pre
+    flow, docs, words = events_data.make_flow(str(tmp_path), n=3000, seed=9)
+    ref = eo.flow_word_counts(open(flow).read())
+    out = tmp_path / "doc_wc.dat"
+    with FlowEvents(flow) as ev:
+        assert ev.word_counts(str(out)) == len(ref)
+        with pytest.raises(_lib.OniError):
+            ev.score_write(1.0, str(tmp_path / "x"))  # no result tables were given
+    assert out.read_text().split("\n")[:-1] == ref
+    assert sum(int(ln.rsplit(",", 1)[1]) for ln in ref) == 2 * len(eo.flow_post(open(flow).read(), "", "", 0.0)["rows"])
+    lda_pre(str(tmp_path) + "/")
+    model = (tmp_path / "model.dat").read_text().split("\n")[:-1]
+    assert len(model) == len({ln.split(",")[0] for ln in ref})  # one document per IP
+    assert sum(int(ln.split(" ")[0]) for ln in model) == len(ref)  # one pair per line, duplicates kept
+    # dns, through the command line (host-only stage: runs without a GPU)
+    dns, top, _, _ = events_data.make_dns(str(tmp_path), n=3000, seed=10)
+    r = subprocess.run([LDA_BIN, "dns_pre", dns, top, str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert out.read_text().split("\n")[:-1] == eo.dns_word_counts(open(dns).read(), open(top).read())

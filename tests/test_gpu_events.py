@@ -63,3 +63,31 @@ def test_dns_scored_file(tmp_path):
                        text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert open(out).read().split("\n")[:-1] == eo.dns_post(*args, tol)["scored"]
+
+
+def test_whole_flow_pipeline_from_the_command_line(tmp_path):
+    """ml_ops.sh:44-108 with every stage replaced by the `lda` executable: raw flows -> doc_wc.dat ->
+    words/doc/model.dat -> EM -> doc_results/word_results -> scored rows."""
+    import events_data
+    flow, _, _ = events_data.make_flow(str(tmp_path), n=5000, seed=31)
+    for name in ("doc_results.csv", "word_results.csv"):
+        p = tmp_path / name
+        if p.exists():
+            p.unlink()
+    d = str(tmp_path) + "/"
+    (tmp_path / "settings.txt").write_text("var max iter 20\nvar convergence 1e-6\nem max iter 5\n"
+                                           "em convergence 1e-4\nalpha estimate\n")
+    env = dict(os.environ, ONI_LDA_SEED="4357")
+    for cmd in (["flow_pre", flow, d + "doc_wc.dat"], ["pre", d],
+                ["est", "2.5", "20", d + "settings.txt", "1", d + "model.dat", "random", str(tmp_path)],
+                ["post", d], ["flow_post", flow, d, "1.0", d + "scored.csv"]):
+        r = subprocess.run([LDA_BIN] + cmd, capture_output=True, text=True, env=env)
+        assert r.returncode == 0, (cmd, r.stdout, r.stderr)
+    got = open(d + "scored.csv").read().split("\n")[:-1]
+    ref = eo.flow_post(open(flow).read(), open(d + "doc_results.csv").read(), open(d + "word_results.csv").read(), 1.0)
+    assert got == ref["scored"] and len(got) == len(ref["rows"]) > 4500
+    keys = [min(float(r.split(",")[-2]), float(r.split(",")[-1])) for r in got]
+    assert keys == sorted(keys) and 0 < keys[0] < keys[-1] < 1
+    # every IP of the day got a topic mix; words longer than 20 bytes miss, as in the reference chain
+    hit = sum(a and b for a, b in ref["doc_hits"])
+    assert hit == len(ref["rows"])
