@@ -153,20 +153,30 @@ __device__ __forceinline__ double group_max(double v, unsigned gmask)
 #define ONI_ESTEP_LAT 1
 #endif
 
-// Resident blocks per SM the register allocation is tuned for (128-thread blocks).
+// Block size and the resident blocks per SM the register allocation is tuned for.
+#ifndef ONI_ESTEP_THREADS
+#define ONI_ESTEP_THREADS 128
+#endif
 #ifndef ONI_ESTEP_MINB
 #define ONI_ESTEP_MINB 3
 #endif
 
+#if defined(ONI_ESTEP_MAXNREG)
+#define ONI_ESTEP_BOUNDS __maxnreg__(ONI_ESTEP_MAXNREG)
+#elif ONI_ESTEP_MINB > 0
+#define ONI_ESTEP_BOUNDS __launch_bounds__(ONI_ESTEP_THREADS, ONI_ESTEP_MINB)
+#else
+#define ONI_ESTEP_BOUNDS __launch_bounds__(ONI_ESTEP_THREADS)
+#endif
 template <int G, int T, bool SHIFT, bool LONGDOC = false>
-__global__ void __launch_bounds__(128, ONI_ESTEP_MINB) estep_kernel(const EstepParams p)
+__global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
 {
     __shared__ MathTables tabs;
     // one document per warp (G = 32): a long document is a serial chain of visits, so this
     // instantiation trades a few instructions for a shorter dependency chain per visit
     // (LONGDOC launches hold only documents of >= 1024 pairs)
     constexpr bool LAT = LONGDOC && (G == 32) && (ONI_ESTEP_LAT != 0);
-    __shared__ double red_buf[LAT ? 4 * 32 : 1];  // per-warp exchange buffer of the sum below
+    __shared__ double red_buf[LAT ? ONI_ESTEP_THREADS : 1];  // per-warp exchange buffer of the sum below
     {
         const double *src = reinterpret_cast<const double *>(&g_math_tables);
         double *dst = reinterpret_cast<double *>(&tabs);
