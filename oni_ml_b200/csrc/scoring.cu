@@ -159,27 +159,26 @@ __device__ __forceinline__ double dot_paired(const double *theta, const double *
         t1[i] = (in && d1 >= 0) ? __ldg(reinterpret_cast<const double2 *>(theta + (size_t)d1 * (2 * CH)) + piece) : fill;
         p1[i] = (in && w1 >= 0) ? __ldg(reinterpret_cast<const double2 *>(pwz + (size_t)w1 * (2 * CH)) + piece) : fill;
     }
-    // hand over and accumulate, piece pair by piece pair: the even lane gives away its piece
-    // 2i of the odd lane's event and receives piece 2i+1 of its own; the odd lane the other way
-    // round.  After exchange i both lanes hold pieces 2i and 2i+1 of their own event, in topic
-    // order: (own, received) for the even lane, (received, own) for the odd one.
+    // hand over and accumulate, piece pair by piece pair.  The lane that loaded a piece also
+    // forms its two products (__dmul_rn: the same rounding wherever it is done), so only the
+    // products travel: the even lane gives away piece 2i of the odd lane's event and receives
+    // piece 2i+1 of its own; the odd lane the other way round.  The owner then adds the
+    // products of pieces 2i and 2i+1 in topic order, unfused.
     double acc = 0.0;
 #pragma unroll
     for (int i = 0; i < HALF; i++) {
-        const double2 give_t = q ? t0[i] : t1[i], give_p = q ? p0[i] : p1[i];
-        const double2 mine_t = q ? t1[i] : t0[i], mine_p = q ? p1[i] : p0[i];
-        double2 got_t, got_p;
-        got_t.x = __shfl_xor_sync(0xffffffffu, give_t.x, 1);
-        got_t.y = __shfl_xor_sync(0xffffffffu, give_t.y, 1);
-        got_p.x = __shfl_xor_sync(0xffffffffu, give_p.x, 1);
-        got_p.y = __shfl_xor_sync(0xffffffffu, give_p.y, 1);
-        const double2 a0 = q ? got_t : mine_t, b0 = q ? got_p : mine_p;  // piece 2i
-        const double2 a1 = q ? mine_t : got_t, b1 = q ? mine_p : got_p;  // piece 2i+1
-        acc = __dadd_rn(acc, __dmul_rn(a0.x, b0.x));
-        acc = __dadd_rn(acc, __dmul_rn(a0.y, b0.y));
+        const double2 ta = q ? t0[i] : t1[i], pa = q ? p0[i] : p1[i];  // the partner's piece
+        const double2 tb = q ? t1[i] : t0[i], pb = q ? p1[i] : p0[i];  // my own piece
+        const double gx = __dmul_rn(ta.x, pa.x), gy = __dmul_rn(ta.y, pa.y);
+        const double mx = __dmul_rn(tb.x, pb.x), my = __dmul_rn(tb.y, pb.y);
+        const double rx = __shfl_xor_sync(0xffffffffu, gx, 1);
+        const double ry = __shfl_xor_sync(0xffffffffu, gy, 1);
+        // piece 2i then piece 2i+1: (own, received) on the even lane, (received, own) on the odd
+        acc = __dadd_rn(acc, q ? rx : mx);
+        acc = __dadd_rn(acc, q ? ry : my);
         if (2 * i + 1 < CH) {
-            acc = __dadd_rn(acc, __dmul_rn(a1.x, b1.x));
-            acc = __dadd_rn(acc, __dmul_rn(a1.y, b1.y));
+            acc = __dadd_rn(acc, q ? mx : rx);
+            acc = __dadd_rn(acc, q ? my : ry);
         }
     }
     return acc;
