@@ -184,8 +184,11 @@ __device__ __forceinline__ double dot_paired(const double *theta, const double *
     return acc;
 }
 
+#ifndef ONI_SCORE_MINB
+#define ONI_SCORE_MINB 4
+#endif
 template <bool FLOW, int CH>
-__global__ void __launch_bounds__(128, 4)
+__global__ void __launch_bounds__(128, ONI_SCORE_MINB)
 score_filter_paired_kernel(const double *__restrict__ theta, const double *__restrict__ pwz, long long n,
                            const int32_t *__restrict__ a_doc, const int32_t *__restrict__ b_doc,
                            const int32_t *__restrict__ a_word, const int32_t *__restrict__ b_word,
