@@ -19,9 +19,9 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #include <algorithm>
-#include <atomic>
 #include <string>
 #include <string_view>
 #include <thread>
@@ -87,6 +87,14 @@ int java_double_str(char *out, double v)
     char *p = out;
     if (signbit(v)) { *p++ = '-'; v = -v; }
     if (v == 0.0) { strcpy(p, "0.0"); return (int)(p - out) + 3; }
+    if (v < 1e7 && v == (double)(int)v) {  // ports, bins, packet counts: "<integer>.0"
+        char tmp[12];
+        int n = 0;
+        for (int u = (int)v; u > 0; u /= 10) tmp[n++] = (char)('0' + u % 10);
+        while (n > 0) *p++ = tmp[--n];
+        *p++ = '.'; *p++ = '0'; *p = 0;
+        return (int)(p - out);
+    }
     char e[40];
     int prec = 0;
     for (prec = 0; prec < 17; prec++) {
@@ -153,6 +161,25 @@ int io_threads()
     int t = e ? atoi(e) : (int)std::thread::hardware_concurrency();
     return std::max(1, std::min(t, 64));
 }
+
+// ONI_LDA_TIMING=1: stage times on stderr
+struct Laps {
+    bool on = getenv("ONI_LDA_TIMING") != nullptr;
+    double t = now();
+    static double now()
+    {
+        struct timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        return ts.tv_sec + 1e-9 * ts.tv_nsec;
+    }
+    void lap(const char *what)
+    {
+        if (!on) return;
+        const double n = now();
+        fprintf(stderr, "[oni events] %-28s %8.1f ms\n", what, 1e3 * (n - t));
+        t = n;
+    }
+};
 
 // fn(lo, hi, tid) over [0, n) in contiguous slices; the first slice's message wins on failure
 template <class F>
@@ -375,8 +402,10 @@ int flow_word(const oni_events &ev, size_t i, char *out)
 
 int flow_open(oni_events &ev)
 {
+    Laps laps;
     std::vector<sv> lines;
     split_lines(ev.data, lines);
+    laps.lap("split lines");
     ev.lines_in = (int64_t)lines.size();
     const size_t n = lines.size();
     // removeHeader (:20-24): every line equal to the first one goes
@@ -404,6 +433,7 @@ int flow_open(oni_events &ev)
             keep[i] = 1;
         }
     }));
+    laps.lap("filter + parse");
     size_t m = 0;
     for (size_t i = 0; i < n; i++)
         if (keep[i]) {
@@ -423,9 +453,10 @@ int flow_open(oni_events &ev)
         tmp = ipkt;
         ecdf_cuts(tmp, QUINT5, 5, ev.cuts[2]);
     }
+    laps.lap("compact + cuts");
     ev.bins.resize(3 * m); ev.word_port.resize(m); ev.flags.resize(m);
     ev.a_doc.resize(m); ev.b_doc.resize(m); ev.a_word.resize(m); ev.b_word.resize(m);
-    return parallel_rows(m, [&](size_t lo, size_t hi, int, std::string &) {
+    const int rc = parallel_rows(m, [&](size_t lo, size_t hi, int, std::string &) {
         std::vector<sv> f;
         char w[160];
         for (size_t i = lo; i < hi; i++) {
@@ -467,6 +498,8 @@ int flow_open(oni_events &ev)
             ev.b_word[i] = lookup(ev.words, (fl & 4) ? marked : plain);  // :231 row(34) dest_word
         }
     });
+    laps.lap("bins + words + lookups");
+    return rc;
 }
 
 // the featurised row as the script holds it just before scoring (columns 0..34)
@@ -662,8 +695,10 @@ int open_common(int kind, const char *events_csv, const char *top_csv, const cha
     if (!ev) return oni_set_error(ONI_ERR_NOMEM, "events_open: out of memory");
     ev->kind = kind;
     int rc = ONI_OK;
+    Laps laps;
     try {
         rc = slurp(events_csv, ev->data);
+        laps.lap("read events file");
         if (rc == ONI_OK && kind == 0) rc = slurp(top_csv, ev->top_text);
         ev->has_tables = doc_results != nullptr;  // absent for the pre-LDA word count
         if (rc == ONI_OK && ev->has_tables) rc = load_table(doc_results, ev->docs);
@@ -792,6 +827,40 @@ extern "C" int oni_events_score_write(oni_events *ev, double tol, const char *ou
 // destination side (row(9), dest_word) separately and writes both lists, so a pair can appear
 // twice (lda_pre.py keeps both).  Spark leaves the line order to its hash partitioner; here:
 // first appearance, source-side list first.
+namespace {
+// (ip, word) without building the word's text: the word is a function of these fields
+struct WKey {
+    sv ip, type, rcode;  // type / rcode: dns only
+    uint64_t u;          // flow: bits of word_port
+    uint32_t v;          // bins, flags
+    bool operator==(const WKey &o) const
+    {
+        return u == o.u && v == o.v && ip == o.ip && type == o.type && rcode == o.rcode;
+    }
+};
+struct WHash {
+    size_t operator()(const WKey &k) const
+    {
+        const std::hash<sv> h;
+        uint64_t x = h(k.ip) * 0x9E3779B97F4A7C15ull ^ k.u;
+        x = (x ^ (x >> 29)) * 0xBF58476D1CE4E5B9ull ^ k.v;
+        if (!k.type.empty() || !k.rcode.empty()) x = (x ^ h(k.type)) * 0x94D049BB133111EBull ^ h(k.rcode);
+        return (size_t)(x ^ (x >> 32));
+    }
+};
+struct WEntry { WKey key; size_t first_row; int64_t count; };
+struct WTable {
+    std::unordered_map<WKey, size_t, WHash> slot;
+    std::vector<WEntry> order;  // first appearance
+    void add(const WKey &k, size_t row, int64_t n)
+    {
+        auto it = slot.find(k);
+        if (it == slot.end()) { slot.emplace(k, order.size()); order.push_back(WEntry{k, row, n}); }
+        else order[it->second].count += n;
+    }
+};
+}  // namespace
+
 extern "C" int oni_events_word_counts(const oni_events *ev, const char *out_path, int64_t *num_lines)
 {
     if (!ev || !out_path) return oni_set_error(ONI_ERR_ARG, "events_word_counts: null argument");
@@ -800,37 +869,74 @@ extern "C" int oni_events_word_counts(const oni_events *ev, const char *out_path
     setvbuf(f, nullptr, _IOFBF, 1 << 20);
     const size_t n = ev->row.size();
     int64_t lines = 0;
-    std::vector<sv> fld;
-    char w[256];
+    Laps laps;
     for (int side = 0; side < (ev->kind ? 2 : 1); side++) {
-        std::unordered_map<std::string, size_t> slot;
-        std::vector<std::pair<std::string, int64_t>> order;
-        std::string key;
-        for (size_t i = 0; i < n; i++) {
-            split_java(ev->row[i], ',', fld);
+        // keys of all rows side by side, then every thread counts the keys whose hash falls in its
+        // share; sorting the distinct pairs by the row that introduced them gives first-appearance order
+        std::vector<WKey> keys(n);
+        std::vector<uint32_t> hv(n);
+        ONI_TRY(parallel_rows(n, [&](size_t lo, size_t hi, int, std::string &) {
+            std::vector<sv> fld;
+            const WHash hasher;
+            for (size_t i = lo; i < hi; i++) {
+                split_java(ev->row[i], ',', fld);
+                WKey k{};
+                if (ev->kind) {
+                    k.ip = fld[8 + side];
+                    memcpy(&k.u, &ev->word_port[i], 8);
+                    k.v = (uint32_t)ev->bins[3 * i] | (uint32_t)ev->bins[3 * i + 1] << 8 |
+                          (uint32_t)ev->bins[3 * i + 2] << 16 | (uint32_t)((ev->flags[i] >> (side ? 2 : 1)) & 1) << 24;
+                } else {
+                    const uint8_t *b = &ev->bins[5 * i];
+                    k.ip = fld[C_IPDST]; k.type = fld[C_TYPE]; k.rcode = fld[C_RCODE];
+                    k.u = (uint64_t)b[0] | (uint64_t)b[1] << 8 | (uint64_t)b[2] << 16 | (uint64_t)b[3] << 24 |
+                          (uint64_t)b[4] << 32;
+                    k.v = ev->top[i];
+                }
+                keys[i] = k;
+                const size_t h = hasher(k);
+                hv[i] = (uint32_t)(h ^ (h >> 32));
+            }
+        }));
+        laps.lap("  row keys");
+        const int T = io_threads();
+        std::vector<std::vector<WEntry>> found(T);
+        {
+            std::vector<std::thread> th;
+            for (int t = 0; t < T; t++)
+                th.emplace_back([&, t] {
+                    WTable mine;
+                    for (size_t i = 0; i < n; i++)
+                        if ((int)((hv[i] >> 8) % (uint32_t)T) == t) mine.add(keys[i], i, 1);
+                    found[t].swap(mine.order);
+                });  // (the table is torn down by its own thread)
+            for (auto &x : th) x.join();
+        }
+        struct { std::vector<WEntry> order; } all;
+        for (int t = 0; t < T; t++) all.order.insert(all.order.end(), found[t].begin(), found[t].end());
+        std::sort(all.order.begin(), all.order.end(),
+                  [](const WEntry &x, const WEntry &y) { return x.first_row < y.first_row; });
+        laps.lap("  count + order");
+        std::vector<sv> fld;
+        char w[256];
+        for (const WEntry &e : all.order) {
+            const size_t i = e.first_row;
+            fwrite(e.key.ip.data(), 1, e.key.ip.size(), f);
+            fputc(',', f);
             if (ev->kind) {
-                key.assign(fld[8 + side]);
-                key += ',';
-                if (ev->flags[i] & (side ? 4 : 2)) key += "-1_";
+                if (ev->flags[i] & (side ? 4 : 2)) fputs("-1_", f);
                 flow_word(*ev, i, w);
             } else {
-                key.assign(fld[C_IPDST]);
-                key += ',';
+                split_java(ev->row[i], ',', fld);
                 dns_word(*ev, i, fld, w);
             }
-            key += w;
-            auto it = slot.find(key);
-            if (it == slot.end()) {
-                slot.emplace(key, order.size());
-                order.emplace_back(key, 1);
-            } else {
-                order[it->second].second++;
-            }
+            fprintf(f, "%s,%lld\n", w, (long long)e.count);
         }
-        for (auto &kv : order) fprintf(f, "%s,%lld\n", kv.first.c_str(), (long long)kv.second);
-        lines += (int64_t)order.size();
+        lines += (int64_t)all.order.size();
+        laps.lap("  write");
     }
     if (fclose(f) != 0) return oni_set_error(ONI_ERR_IO, "write failed on %s", out_path);
+    laps.lap("word counts");
     if (num_lines) *num_lines = lines;
     return ONI_OK;
 }
