@@ -24,6 +24,7 @@
 
 #include <algorithm>
 #include <numeric>
+#include <thread>
 #include <vector>
 
 #include "common.h"
@@ -511,17 +512,28 @@ void oni_internal_random_model(int K, int V, uint32_t seed, std::vector<double> 
 {
     CokusMT mt(seed);
     logbeta.assign((size_t)K * V, 0.0);
-    std::vector<double> cw((size_t)V);
+    std::vector<double> lct((size_t)K);
+    // the draws and the running totals are one sequential stream (k outer, n inner) ...
     for (int k = 0; k < K; k++) {
         double ct = 0.0;
+        double *cw = &logbeta[(size_t)k * V];
         for (int n = 0; n < V; n++) {
             cw[n] = 1.0 / V + mt.uniform();
             ct += cw[n];
         }
-        const double lct = log(ct);
-        for (int n = 0; n < V; n++)
-            logbeta[(size_t)k * V + n] = (cw[n] > 0) ? log(cw[n]) - lct : -100.0;
+        lct[k] = log(ct);
     }
+    // ... the K*V logarithms after them are independent: topics over host threads (same libm)
+    const int T = std::max(1, std::min<int>({K, (int)std::thread::hardware_concurrency(), 16}));
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; t++)
+        th.emplace_back([&, t] {
+            for (int k = t; k < K; k += T) {
+                double *cw = &logbeta[(size_t)k * V];
+                for (int n = 0; n < V; n++) cw[n] = (cw[n] > 0) ? log(cw[n]) - lct[k] : -100.0;
+            }
+        });
+    for (auto &x : th) x.join();
 }
 
 extern "C" int oni_lda_init_random(oni_lda_ctx *c, uint32_t seed, double alpha)

@@ -160,13 +160,22 @@ class LdaEngine:
         check(self._L.oni_lda_comm_init(self._h, C.addressof(buf), rank, nranks))
 
     # -- readback ----------------------------------------------------------
-    def logbeta(self) -> np.ndarray:
-        out = np.zeros((self.num_topics, self.num_terms))
+    def _out(self, out, shape):
+        if out is None:
+            return np.empty(shape)
+        if out.shape != shape or out.dtype != np.float64 or not out.flags["C_CONTIGUOUS"]:
+            raise ValueError("out must be a C-contiguous float64 array of shape %r" % (shape,))
+        return out
+
+    def logbeta(self, out: np.ndarray | None = None) -> np.ndarray:
+        """final.beta values [K][V]; `out` (e.g. a pinned buffer the caller reuses) is filled in place."""
+        out = self._out(out, (self.num_topics, self.num_terms))
         check(self._L.oni_lda_get_logbeta(self._h, out.ctypes.data))
         return out
 
-    def gamma(self) -> np.ndarray:
-        out = np.zeros((self.num_docs, self.num_topics))
+    def gamma(self, out: np.ndarray | None = None) -> np.ndarray:
+        """final.gamma values [D][K]; `out` as for logbeta."""
+        out = self._out(out, (self.num_docs, self.num_topics))
         check(self._L.oni_lda_get_gamma(self._h, out.ctypes.data))
         return out
 
