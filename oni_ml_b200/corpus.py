@@ -88,12 +88,17 @@ def write_model_dat(path: str, c: Corpus) -> None:
 def synth_corpus(num_docs: int, num_terms: int, k_true: int = 20, mu: float = 2.5,
                  sigma: float = 1.0, geom_p: float = 0.25, dup_frac: float = 0.02,
                  seed: int = 20160122, device: str | torch.device = "cpu",
-                 as_torch: bool = False):
+                 as_torch: bool = False, topic_seed: int | None = None):
     """Synthetic corpus of SURVEY.md section 8(d).
 
     Returns a :class:`Corpus` (numpy, host) or, with ``as_torch=True``, the three
     tensors ``(doc_ptr int64, word int32, count int32)`` on ``device`` so a
     flow-day sized corpus can be generated in HBM without a host round trip.
+
+    ``topic_seed`` draws the topics from their own stream, so that the shards of a
+    multi-GPU run (different ``seed`` per rank) are documents of ONE corpus: same
+    topics, different documents.  ``None`` keeps the single-stream behaviour the
+    committed fixtures were generated with.
     """
     dev = torch.device(device)
     g = torch.Generator(device=dev)
@@ -107,8 +112,13 @@ def synth_corpus(num_docs: int, num_terms: int, k_true: int = 20, mu: float = 2.
 
     # topics: Dirichlet(0.05) shaped by a Zipf(1.05) envelope over a permuted vocabulary
     zipf = 1.0 / torch.arange(1, V + 1, dtype=f64, device=dev) ** 1.05
+    g_docs = g
+    if topic_seed is not None:
+        g = torch.Generator(device=dev)
+        g.manual_seed(topic_seed)
     perm = torch.randperm(V, generator=g, device=dev)
     beta = gamma_sample((K, V), 0.05) * zipf[perm][None, :] + 1e-300
+    g = g_docs
     beta /= beta.sum(1, keepdim=True)
     cdf = torch.cumsum(beta, 1)
     cdf = cdf / cdf[:, -1:]
