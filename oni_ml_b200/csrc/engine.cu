@@ -98,10 +98,12 @@ struct oni_lda_ctx {
     int T_long = 0;
     int long_min = 0;      // documents with at least this many pairs are "long" (0 = none)
     int32_t n_long = 0;    // they are the first n_long entries of `order`
+    int32_t n_excl = 0;    // the first n_excl of those get an SM to themselves (4 documents per SM)
     oni_lda_settings st{};
     int var_max_iter = 0;  // doubles when the bound decreases (lda-estimate.c:261)
-    cudaStream_t stream = nullptr, stream_long = nullptr;
-    cudaEvent_t ev[6] = {}, ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t stream = nullptr, stream_long = nullptr, stream_excl = nullptr;
+    cudaEvent_t ev[6] = {}, ev_fork = nullptr, ev_join = nullptr, ev_join_excl = nullptr,
+                ev_t_long = nullptr, ev_t_excl = nullptr, ev_t_main = nullptr;  // ONI_LDA_TIMING: ends of the three launches
     int sm_count = 0;
 
     // corpus shard
@@ -175,7 +177,7 @@ void free_corpus(oni_lda_ctx *c)
     c->d_perm = nullptr; c->d_items = c->d_items2 = nullptr; c->d_phi = nullptr;
     c->d_gamma = c->d_doc_lik = c->d_doc_ass = nullptr; c->d_doc_iters = nullptr;
     c->d_partial = nullptr;
-    c->D = 0; c->nnz = 0; c->n_long = 0;
+    c->D = 0; c->nnz = 0; c->n_long = 0; c->n_excl = 0;
 }
 
 double now_seconds();
@@ -209,10 +211,23 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     int32_t n_long = 0;
     if (c->long_min > 0)
         for (int32_t d = 0; d < D; d++) n_long += (h_ptr[d + 1] - h_ptr[d]) >= c->long_min;
+    // A document long enough for its serial chain of word visits to outlast the rest of the
+    // E-step sets the pace of the whole launch, and twice over when its warp shares a scheduler
+    // with busy warps.  The few longest documents therefore get SMs to themselves.  Default
+    // threshold: 1/20000 of the shard's pairs (what a chain can cover while the rest runs);
+    // at most 1/8 of the SMs are given away.  ONI_LDA_EXCL_DOC overrides (0 = off).
+    int32_t n_excl = 0;
+    if (n_long > 0 && c->G_long == 32 && c->T_long <= 4) {
+        const char *env = getenv("ONI_LDA_EXCL_DOC");
+        const int64_t excl_min = env ? atoll(env) : std::max<int64_t>(c->long_min, nnz / 20000);
+        if (excl_min > 0)
+            for (int32_t d = 0; d < D; d++) n_excl += (h_ptr[d + 1] - h_ptr[d]) >= excl_min;
+        n_excl = std::min<int32_t>({n_excl, n_long, 4 * std::max(1, c->sm_count / 8)});
+    }
     tm.lap("validate doc_ptr");
 
     free_corpus(c);
-    c->D = D; c->nnz = nnz; c->n_long = n_long;
+    c->D = D; c->nnz = nnz; c->n_long = n_long; c->n_excl = n_excl;
     cudaStream_t s = c->stream;
     ONI_TRY(dev_alloc(&c->d_tok, (size_t)nnz));
     ONI_TRY(dev_alloc(&c->d_doc_ptr, (size_t)D + 1));
@@ -407,6 +422,9 @@ static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_setti
     c->sm_count = prop.multiProcessorCount;
     ONI_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     ONI_CUDA(cudaStreamCreateWithFlags(&c->stream_long, cudaStreamNonBlocking));
+    ONI_CUDA(cudaStreamCreateWithFlags(&c->stream_excl, cudaStreamNonBlocking));
+    ONI_CUDA(cudaEventCreateWithFlags(&c->ev_join_excl, cudaEventDisableTiming));
+    ONI_CUDA(cudaEventCreate(&c->ev_t_long)); ONI_CUDA(cudaEventCreate(&c->ev_t_excl)); ONI_CUDA(cudaEventCreate(&c->ev_t_main));
     for (auto &e : c->ev) ONI_CUDA(cudaEventCreate(&e));
     ONI_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     ONI_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
@@ -415,6 +433,8 @@ static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_setti
     if (G < 32) {
         const char *env = getenv("ONI_LDA_LONG_DOC");
         c->long_min = env ? atoi(env) : 1024;
+        if (c->long_min > 0 && c->long_min < 64) c->long_min = 64;  // the long-document build requests rows 16 visits ahead
+        if (c->long_min > 0 && c->long_min < 16) c->long_min = 16;  // the long-document build queues rows several visits ahead
         const char *g = getenv("ONI_LDA_LONG_G");  // tuning knob: 8, 16 or 32
         c->G_long = (g && (atoi(g) == 8 || atoi(g) == 16) && atoi(g) > G) ? atoi(g) : 32;
         c->T_long = (K + c->G_long - 1) / c->G_long;
@@ -424,7 +444,7 @@ static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_setti
     ONI_TRY(dev_alloc(&c->d_alpha, 1));
     ONI_TRY(dev_alloc(&c->d_ss, c->ss_count()));
     ONI_TRY(dev_alloc(&c->d_block_partial, (size_t)DOC_RED_BLOCKS * 3));
-    ONI_TRY(dev_alloc(&c->d_ticket, 2));
+    ONI_TRY(dev_alloc(&c->d_ticket, 3));
     ONI_TRY(dev_alloc(&c->d_done, 1));
     ONI_TRY(dev_alloc(&c->d_nan, 1));
     ONI_CUDA(cudaMemset(c->d_done, 0, sizeof(unsigned)));
@@ -447,6 +467,11 @@ extern "C" void oni_lda_destroy(oni_lda_ctx *c)
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->stream_long) cudaStreamDestroy(c->stream_long);
+    if (c->stream_excl) cudaStreamDestroy(c->stream_excl);
+    if (c->ev_join_excl) cudaEventDestroy(c->ev_join_excl);
+    if (c->ev_t_long) cudaEventDestroy(c->ev_t_long);
+    if (c->ev_t_excl) cudaEventDestroy(c->ev_t_excl);
+    if (c->ev_t_main) cudaEventDestroy(c->ev_t_main);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -574,21 +599,37 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
     // is hugely negative, i.e. alpha tiny; then use the max-shifted kernel.
     const bool shift = !(c->alpha > 0.01);
 
-    ONI_CUDA(cudaMemsetAsync(c->d_ticket, 0, 2 * sizeof(unsigned), s));
+    ONI_CUDA(cudaMemsetAsync(c->d_ticket, 0, 3 * sizeof(unsigned), s));
     ONI_CUDA(cudaEventRecord(c->ev[0], s));
-    if (c->n_long > 0) {
-        // long documents first, one per warp, on a second stream so that the rest of
+    if (c->n_long > 0) ONI_CUDA(cudaEventRecord(c->ev_fork, s));
+    if (c->n_excl > 0) {
+        // the very longest documents before anything else, on SMs nothing else will share
+        ONI_CUDA(cudaStreamWaitEvent(c->stream_excl, c->ev_fork, 0));
+        EstepParams px = p;
+        px.D = c->n_excl;
+        px.ticket = c->d_ticket + 2;
+        cudaError_t e = launch_estep(c->G_long, c->T_long, shift, px, c->sm_count, c->stream_excl, /*longdoc=*/true,
+                                     /*exclusive_blocks=*/(c->n_excl + 3) / 4);
+        if (e != cudaSuccess)
+            return oni_set_error(ONI_ERR_CUDA, "E-step launch (exclusive, T=%d): %s", c->T_long, cudaGetErrorString(e));
+        c->launches++;
+        ONI_CUDA(cudaEventRecord(c->ev_join_excl, c->stream_excl));
+        ONI_CUDA(cudaEventRecord(c->ev_t_excl, c->stream_excl));
+    }
+    if (c->n_long > c->n_excl) {
+        // long documents next, one per warp, on a second stream so that the rest of
         // the corpus fills the SMs as these drain
-        ONI_CUDA(cudaEventRecord(c->ev_fork, s));
         ONI_CUDA(cudaStreamWaitEvent(c->stream_long, c->ev_fork, 0));
         EstepParams pl = p;
-        pl.D = c->n_long;
+        pl.order = c->d_order + c->n_excl;
+        pl.D = c->n_long - c->n_excl;
         pl.ticket = c->d_ticket + 1;
         cudaError_t e = launch_estep(c->G_long, c->T_long, shift, pl, c->sm_count, c->stream_long, /*longdoc=*/true);
         if (e != cudaSuccess)
             return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=%d,T=%d): %s", c->G_long, c->T_long, cudaGetErrorString(e));
         c->launches++;
         ONI_CUDA(cudaEventRecord(c->ev_join, c->stream_long));
+        ONI_CUDA(cudaEventRecord(c->ev_t_long, c->stream_long));
     }
     if (c->D > c->n_long) {
         EstepParams ps = p;
@@ -599,7 +640,9 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
             return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=%d,T=%d): %s", c->G, c->T, cudaGetErrorString(e));
         c->launches++;
     }
-    if (c->n_long > 0) ONI_CUDA(cudaStreamWaitEvent(s, c->ev_join, 0));
+    ONI_CUDA(cudaEventRecord(c->ev_t_main, s));
+    if (c->n_long > c->n_excl) ONI_CUDA(cudaStreamWaitEvent(s, c->ev_join, 0));
+    if (c->n_excl > 0) ONI_CUDA(cudaStreamWaitEvent(s, c->ev_join_excl, 0));
     ONI_CUDA(cudaEventRecord(c->ev[1], s));
     ONI_TRY(dispatch_ss(c));
     {
@@ -689,6 +732,14 @@ static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
     c->stats.word_visits = (int64_t)c->h_pinned[3];
     float ms = 0;
     if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) c->stats.ms_estep_kernel = ms;
+    if (getenv("ONI_LDA_TIMING")) {
+        float a = -1, b = -1, m = -1;
+        if (c->n_excl > 0) cudaEventElapsedTime(&a, c->ev[0], c->ev_t_excl);
+        if (c->n_long > c->n_excl) cudaEventElapsedTime(&b, c->ev[0], c->ev_t_long);
+        cudaEventElapsedTime(&m, c->ev[0], c->ev_t_main);
+        fprintf(stderr, "[oni lda] E-step %.2f ms: exclusive (%d docs) done at %.2f, long (%d docs) at %.2f, rest at %.2f\n",
+                c->stats.ms_estep_kernel, c->n_excl, a, c->n_long - c->n_excl, b, m);
+    }
     if (cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]) == cudaSuccess) c->stats.ms_suffstats = ms;
     if (cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]) == cudaSuccess) c->stats.ms_mstep = ms;
     c->stats.kernel_launches = c->launches;

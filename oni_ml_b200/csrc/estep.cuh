@@ -140,6 +140,17 @@ __device__ __forceinline__ double group_max(double v, unsigned gmask)
     return v;
 }
 
+// Asynchronous 8-byte copy global -> shared (LDGSTS): nothing waits on a register, so a row can
+// be requested many visits ahead without a scoreboard stall when it is next touched.
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gsrc)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // ---------------------------------------------------------------- the kernel
 // A group that reaches the end of its sweep waits up to this many word visits for the
 // other groups of its warp, so that their end-of-sweep sections (bound, convergence
@@ -151,6 +162,15 @@ __device__ __forceinline__ double group_max(double v, unsigned gmask)
 // Latency-tuned arithmetic in the one-document-per-warp instantiation (0 = off).
 #ifndef ONI_ESTEP_LAT
 #define ONI_ESTEP_LAT 1
+#endif
+
+// Long-document build: rows and pairs arrive through a shared-memory ring filled by asynchronous
+// copies requested 8/T visits ahead (0 = the one-visit-ahead register loads of the main kernel).
+// With the main kernel streaming phi through HBM a row takes ~1700 cycles to arrive, two visits
+// of a lone document; register loads cannot run further ahead than the first instruction that
+// moves them, the ring can.
+#ifndef ONI_ESTEP_LAT_RING
+#define ONI_ESTEP_LAT_RING 1
 #endif
 
 // Block size and the resident blocks per SM the register allocation is tuned for.
@@ -179,6 +199,13 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
     // (LONGDOC launches hold only documents of >= 1024 pairs)
     constexpr bool LAT = LONGDOC && (G == 32) && (ONI_ESTEP_LAT != 0);
     __shared__ double red_buf[LAT ? ONI_ESTEP_THREADS : 1];  // per-warp exchange buffer of the sum below
+    constexpr bool RING = LAT && (ONI_ESTEP_LAT_RING != 0) && T <= 4;
+    constexpr int QD = (T == 1) ? 8 : (T == 2) ? 4 : 2;  // visits ahead for the rows
+    constexpr int QT = 2 * QD;                           // ... and for the pairs (their addresses)
+    constexpr int NW = ONI_ESTEP_THREADS / 32;
+    __shared__ double ring_lb[RING ? NW * QD * T * 32 : 1];   // [warp][slot][t][lane]
+    __shared__ double ring_old[RING ? NW * QD * T * 32 : 1];
+    __shared__ int2 ring_tk[RING ? NW * QT * 32 : 1];         // [warp][slot][lane] (every lane its own copy)
     {
         const double *src = reinterpret_cast<const double *>(&g_math_tables);
         double *dst = reinterpret_cast<double *>(&tabs);
@@ -192,6 +219,10 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
     const int lead = lane & ~(G - 1);
     const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << lead);
     const int K = p.K, KP = p.KP;
+    double *const my_lb = ring_lb + (RING ? (threadIdx.x >> 5) * QD * T * 32 + lane : 0);
+    double *const my_old = ring_old + (RING ? (threadIdx.x >> 5) * QD * T * 32 + lane : 0);
+    int2 *const my_tk = ring_tk + (RING ? (threadIdx.x >> 5) * QT * 32 + lane : 0);
+    int vi = 0;  // RING: visits of the current document so far (ring slots are vi mod QD / QT)
     const double alpha = *p.alpha;
     const double inv_k = 1.0 / (double)K;
     // lda-inference.c:105-108
@@ -237,7 +268,24 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
                     gam[t] = ok ? g0 : 1.0;
                     dg[t] = ok ? d0 : 0.0;
                 }
-                if (beg < end) {
+                if (RING) {
+                    // (a long document has far more than QT pairs)
+                    cp_async_wait<0>();  // nothing of the previous document may still land in the ring
+                    vi = 0;
+#pragma unroll
+                    for (int i = 0; i < QT; i++) cp_async8(my_tk + i * 32, p.tok + beg + i);
+                    cp_async_commit();
+                    cp_async_wait<0>();
+#pragma unroll
+                    for (int i = 0; i < QD; i++) {
+                        const int2 ti = my_tk[i * 32];
+                        const double *r = p.logbeta_t + (size_t)ti.x * KP;
+#pragma unroll
+                        for (int t = 0; t < T; t++)
+                            cp_async8(my_lb + (i * T + t) * 32, r + (((t < T - 1) || last_ok) ? j + G * t : 0));
+                        cp_async_commit();  // one group per visit: visit 0 waits for the first only
+                    }
+                } else if (beg < end) {
                     // prime the one-visit-ahead pipeline (first sweep: old phi = 1/K)
                     tk = __ldg(p.tok + beg);
                     tk1 = __ldg(p.tok + ((beg + 1 < end) ? beg + 1 : beg));
@@ -256,6 +304,34 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
 
         if (have && pos < end) {
             // ---- one word visit (lda-inference.c:50-75)
+            if (RING) {
+                // this visit's pair and rows out of the ring (requested QD visits ago), then the
+                // request for the visit QD ahead into the slots just read
+                cp_async_wait<QD - 1>();
+                const int st = vi & (QT - 1), sr = vi & (QD - 1);
+                tk = my_tk[st * 32];
+#pragma unroll
+                for (int t = 0; t < T; t++) {
+                    lbc[t] = my_lb[(sr * T + t) * 32];
+                    oldc[t] = my_old[(sr * T + t) * 32];  // (not used during the first sweep)
+                }
+                const int64_t len = end - beg;
+                const int64_t rpos = (pos + QD < end) ? pos + QD : pos + QD - len;
+                const int64_t tpos = (pos + QT < end) ? pos + QT : pos + QT - len;
+                const int2 rtk = my_tk[((vi + QD) & (QT - 1)) * 32];
+                const double *nlb = p.logbeta_t + (size_t)rtk.x * KP;
+                const double *nph = p.phi + (size_t)rpos * KP;
+                const bool row_first_sweep = (pass == 0) && (pos + QD < end);
+#pragma unroll
+                for (int t = 0; t < T; t++) {
+                    const int k = ((t < T - 1) || last_ok) ? j + G * t : 0;
+                    cp_async8(my_lb + (sr * T + t) * 32, nlb + k);
+                    if (!row_first_sweep) cp_async8(my_old + (sr * T + t) * 32, nph + k);
+                }
+                cp_async8(my_tk + st * 32, p.tok + tpos);
+                cp_async_commit();
+                vi++;
+            }
             const double c = (double)tk.y;
             double *phrow = p.phi + (size_t)pos * KP;
             // Software pipeline: the rows of the NEXT visit (wrapping to the first word
@@ -263,7 +339,8 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             // their latency hides behind this visit's arithmetic.
             const int64_t npos = (pos + 1 < end) ? pos + 1 : beg;
             const int64_t n2pos = (npos + 1 < end) ? npos + 1 : beg;
-            const int2 tk2 = __ldg(p.tok + n2pos);
+            int2 tk2 = make_int2(0, 0);
+            if (!RING) tk2 = __ldg(p.tok + n2pos);
             if (ONI_ESTEP_PF_AHEAD > 0 && pass > 0 && j * 128 < KP * 8 + 127) {
                 // the phi rows stream from HBM (every sweep rereads what the last one wrote);
                 // pull the row of a later visit into L2 so the register load above finds it there
@@ -272,7 +349,7 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             }
             const bool next_first_sweep = (pass == 0) && (npos != beg);
             double lbn[T], oldn[T] = {};
-            {
+            if (!RING) {
                 const double *nlb = p.logbeta_t + (size_t)tk1.x * KP;
                 const double *nph = p.phi + (size_t)npos * KP;
 #pragma unroll
@@ -354,10 +431,12 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             for (int t = 0; t < T; t++)
                 if ((t < T - 1) || last_ok) phrow[j + G * t] = x[t];
             // rotate the pipeline
+            if (!RING) {
 #pragma unroll
-            for (int t = 0; t < T; t++) {
-                lbc[t] = lbn[t];
-                oldc[t] = oldn[t];
+                for (int t = 0; t < T; t++) {
+                    lbc[t] = lbn[t];
+                    oldc[t] = oldn[t];
+                }
             }
             // one-word document: the row just written is the next "old".  (Compiled out of the
             // long-document kernel: it becomes a select on the in-flight load and cost a lone
@@ -366,8 +445,10 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
 #pragma unroll
                 for (int t = 0; t < T; t++) oldc[t] = x[t];
             }
-            tk = tk1;
-            tk1 = tk2;
+            if (!RING) {
+                tk = tk1;
+                tk1 = tk2;
+            }
             acc_a = fma(c, a, acc_a);
             if (SHIFT) acc_s = fma(c, shift, acc_s);  // log S_n = shift + log(sum)
             // log S_n is needed once per visit: lane (n mod G) keeps S_n and the

@@ -4,9 +4,10 @@
 namespace oni {
 
 cudaError_t launch_estep(int G, int T, bool shift, const EstepParams &p, int sm_count,
-                         cudaStream_t stream, bool longdoc)
+                         cudaStream_t stream, bool longdoc, int exclusive_blocks)
 {
-    if (longdoc && G == 32 && T <= 4) return launch_estep_g32_long(T, shift, p, sm_count, stream);
+    if (longdoc && G == 32 && T <= 4) return launch_estep_g32_long(T, shift, p, sm_count, stream, exclusive_blocks);
+    if (exclusive_blocks > 0) return cudaErrorInvalidValue;
     switch (G) {
         case 1: return launch_estep_g1(T, shift, p, sm_count, stream);
         case 2: return launch_estep_g2(T, shift, p, sm_count, stream);

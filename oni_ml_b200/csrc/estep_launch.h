@@ -12,8 +12,11 @@ namespace oni {
 // Returns cudaErrorInvalidValue for anything else.
 // longdoc = the launch holds only long documents (>= 1024 pairs): selects the latency-tuned
 // build of the G = 32 kernel (T <= 4), otherwise ignored.
+// exclusive_blocks > 0 (long-document build only): launch that many blocks, each asking for all
+// the shared memory of an SM, so that no other block shares the SM with them and the serial
+// chain of a very long document runs at the speed of a warp that has its scheduler to itself.
 cudaError_t launch_estep(int G, int T, bool shift, const EstepParams &p, int sm_count,
-                         cudaStream_t stream, bool longdoc = false);
+                         cudaStream_t stream, bool longdoc = false, int exclusive_blocks = 0);
 
 cudaError_t launch_estep_g1(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 cudaError_t launch_estep_g2(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
@@ -21,6 +24,7 @@ cudaError_t launch_estep_g4(int T, bool shift, const EstepParams &p, int sm_coun
 cudaError_t launch_estep_g8(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 cudaError_t launch_estep_g16(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 cudaError_t launch_estep_g32(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
-cudaError_t launch_estep_g32_long(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
+cudaError_t launch_estep_g32_long(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s,
+                                  int exclusive_blocks);
 
 }  // namespace oni
