@@ -299,7 +299,10 @@ def _our_arm(args):
     D, V = args.docs or WORKLOAD["docs_per_gpu"], WORKLOAD["vocab"]
     ptr, word, count = synth_corpus(D, V, k_true=K_TOPICS, mu=WORKLOAD["mu"], geom_p=WORKLOAD["geom_p"],
                                     dup_frac=shape.get("dup_frac", 0.02), seed=20160123 + rank, device=dev,
-                                    as_torch=True, topic_seed=20160123)  # ranks hold shards of one corpus
+                                    as_torch=True,
+                                    # ranks hold shards of ONE corpus: rank 0's single stream draws the topics
+                                    # first, the other ranks draw the same topics from a stream of their own
+                                    topic_seed=None if rank == 0 else 20160123)
     nnz = int(word.numel())
     tokens = int(count.sum(dtype=torch.int64))
     st = _lib.Settings(20, 1e-6, 10_000, 1e-6, 1)  # shipped thresholds; the loop count is ours
