@@ -73,7 +73,7 @@ bool parse_double(sv f, double *out)
     const double v = strtod(buf, &end);
     if (end == buf) return false;
     if (*end == 'd' || *end == 'D' || *end == 'f' || *end == 'F') end++;  // Java's type suffixes
-    if (*end) return false;
+    if (*end || v != v) return false;  // (a NaN would poison the sort behind the cut vectors)
     *out = v;
     return true;
 }
@@ -788,6 +788,13 @@ extern "C" int oni_events_score_write(oni_events *ev, double tol, const char *ou
     if (!ev->has_tables)
         return oni_set_error(ONI_ERR_ARG, "events_score_write: opened without doc_results.csv / word_results.csv");
     const int64_t n = (int64_t)ev->row.size();
+    if (n == 0) {  // nothing survived the filters: an empty result, no GPU work
+        FILE *f0 = fopen(out_path, "w");
+        if (!f0) return oni_set_error(ONI_ERR_IO, "cannot write %s: %s", out_path, strerror(errno));
+        fclose(f0);
+        if (num_scored) *num_scored = 0;
+        return ONI_OK;
+    }
     std::vector<int64_t> idx((size_t)std::max<int64_t>(n, 1));
     std::vector<double> key(idx.size()), sa(idx.size()), sb(idx.size());
     int64_t total = 0;

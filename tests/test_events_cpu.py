@@ -96,6 +96,7 @@ def test_flow_tiny_and_degenerate_inputs(tmp_path):
         with FlowEvents(str(p), str(docs), str(words)) as ev:
             assert ev.info()["rows"] == 0
             assert all((v == 0).all() for v in ev.cuts().values())
+            assert ev.score_write(1.0, str(tmp_path / "none.csv")) == 0 and (tmp_path / "none.csv").read_text() == ""
     # one row: its own values sit at ecdf 1.0, above every quantile -> cuts stay 0, bins count cuts below the value
     rnd = random.Random(1)
     row = events_data.flow_row(rnd, ["1.1.1.1", "2.2.2.2"])

@@ -80,6 +80,37 @@ def test_single_e_step_matches_oracle(c0_corpus, k, alpha, vmax):
     assert stats["word_visits"] == ref["word_visits"]
 
 
+@pytest.mark.parametrize("k,alpha", [(20, 2.5), (50, 0.3), (100, 0.2), (20, 0.004)])
+def test_long_document_paths_match_oracle(monkeypatch, k, alpha):
+    """The one-document-per-warp build (rows through the cp.async ring, requested 8/4/2 visits ahead
+    for 1/2/4 topics per lane) and its exclusive-SM launch, forced onto documents of 64..700 pairs
+    (lengths right at the ring's wrap-around limits included), beside ordinary short documents."""
+    monkeypatch.setenv("ONI_LDA_LONG_DOC", "64")
+    monkeypatch.setenv("ONI_LDA_EXCL_DOC", "300")
+    rng = np.random.default_rng(11)
+    V = 400
+    lens = [64, 65, 66, 71, 72, 80, 127, 128, 129, 300, 301, 450, 700] + rng.integers(1, 64, 120).tolist()
+    ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    word = rng.integers(0, V, int(ptr[-1])).astype(np.int32)
+    word[:V] = np.arange(V, dtype=np.int32) % V  # every word id occurs
+    count = rng.geometric(0.3, int(ptr[-1])).astype(np.int32)
+    c = Corpus(ptr, word, count, V)
+    st = _lib.Settings(20, 1e-6, 20, 1e-6, 1)
+    with lda.LdaEngine(0, k, V, st) as eng:
+        eng.set_corpus(c)
+        eng.init_random(99, alpha)
+        lb0 = eng.logbeta()
+        ref = pyoracle.e_step(c, k, alpha, lb0, 20, 1e-6)
+        lik, _ = eng.em_iteration()
+        gam, it1 = eng.gamma(), eng.doc_iters()
+        lik2, _ = eng.em_iteration()  # a second E-step on the same handle: rings and tickets re-primed
+        launches = eng.stats()["kernel_launches"]
+    assert rel_err(gam, ref["gamma"]) < 1e-9
+    assert abs(lik - ref["lik"]) / abs(ref["lik"]) < 1e-11
+    assert int((np.diff(ptr) * it1).sum()) == ref["word_visits"]
+    assert lik2 > lik and launches > 0
+
+
 def _check_against_golden(d, r, k, v, names):
     if "likelihood.dat" in names:
         want = files.read_likelihood(os.path.join(d, "likelihood.dat"))
