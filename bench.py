@@ -24,6 +24,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import shutil
 import statistics
@@ -486,12 +487,19 @@ def _score_arm(args):
 
     def draw(lim, skew):
         u = torch.rand(n, generator=g, device=dev)
-        if skew:
+        if skew == "cube":
             u = u ** 3  # a few hot words, as a Zipf-like vocabulary gives
-        a = (u * lim).to(torch.int32).clamp_(0, lim - 1)
+            a = (u * lim).to(torch.int32)
+        elif skew == "zipf":
+            # Zipf(1.0) over [1, lim]: the continuous inverse CDF is lim^u (rank r has mass ~ 1/r)
+            a = (torch.exp(u.double() * math.log(lim)) - 1.0).to(torch.int32)
+        else:
+            a = (u * lim).to(torch.int32)
+        a.clamp_(0, lim - 1)
         a[torch.rand(n, generator=g, device=dev) < 1e-3] = -1  # lookup misses
         return a
-    ev = [draw(D, False), draw(D, False), draw(V, True), draw(V, True)]
+    doc_skew = "zipf" if args.doc_dist == "zipf" else None  # uniform = worst-case locality
+    ev = [draw(D, doc_skew), draw(D, doc_skew), draw(V, "cube"), draw(V, "cube")]
     ctx = scoring.ScoreContext(theta, pwz, 0)
     # threshold at the 1e-3 quantile of a 2M-event sample (so the sort has ~n/1000 keys)
     m = min(n, 2_000_000)
@@ -539,13 +547,15 @@ def _score_arm(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "post-LDA flow scoring (BASELINE configs[4] shape): %d events, theta %dx%d, p(w|z) %dx%d, "
                                "threshold at the 1e-3 score quantile (%d survivors ranked); one step = all events"
-                               % (n, D, K, V, K, surv), "events": n, "threshold": tol,
+                               % (n, D, K, V, K, surv) + ("; documents Zipf(1.0)" if args.doc_dist == "zipf" else
+                                                          "; documents uniform (worst-case locality)"),
+                   "events": n, "threshold": tol, "doc_dist": args.doc_dist,
                    "l2": "event indices (16 B/event) and the 160 MB theta table exceed the L2"},
         "e2e": {"value": n / e2e_s, "unit": "events/s", "h2d_bytes_per_step": 16 * n + theta.nbytes + pwz.nbytes,
                 "d2h_bytes_per_step": 16 * min(surv, 1_000_000), "seconds": e2e_s,
                 "what": "oni_score_flow over host arrays (tables + event indices uploaded inside)"},
         "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / args.steps * 1e3,
-        "roofline": {"bound": "hbm", "kernel": "score_filter_kernel<flow>", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "score_filter_paired_kernel<flow,10>", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": int(286.3 * n),
                      "traffic_source": "ncu dram__bytes_read per event (profiles/r1_score.txt) x events",
                      "peak_source": peak_src,
@@ -568,6 +578,8 @@ def main():
     ap.add_argument("--workload", default="em", choices=["em", "score"],
                     help="em (default, the headline metric) or score (BASELINE configs[4])")
     ap.add_argument("--events", type=int, default=250_000_000, help="events for --workload score")
+    ap.add_argument("--doc-dist", default="uniform", choices=["uniform", "zipf"],
+                    help="--workload score: how events pick their documents (zipf = Zipf(1.0), the locality variant)")
     ap.add_argument("--shape", default="flow_day", choices=sorted(SHAPES),
                     help="EM corpus shape: flow_day (default, the headline), dns_day, month")
     args = ap.parse_args()
