@@ -186,6 +186,40 @@ __global__ void __launch_bounds__(256) mle_beta_kernel(const double *class_word,
     }
 }
 
+// Layout change between the reference's topic-major model [K][V] (lda.h:40-47, final.beta) and the
+// word-major table the E-step gathers from [V][KP] (padding columns 0).  32x32 tiles through shared
+// memory so that both sides are read and written in whole lines.
+__global__ void __launch_bounds__(256) model_to_word_major_kernel(const double *kv, int32_t K, int32_t V,
+                                                                  int32_t KP, double *vk)
+{
+    __shared__ double tile[32][33];
+    const int w0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int k = k0 + r, w = w0 + threadIdx.x;
+        tile[r][threadIdx.x] = (k < K && w < V) ? kv[(size_t)k * V + w] : 0.0;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int w = w0 + r, k = k0 + threadIdx.x;
+        if (w < V && k < KP) vk[(size_t)w * KP + k] = tile[threadIdx.x][r];
+    }
+}
+__global__ void __launch_bounds__(256) model_to_topic_major_kernel(const double *vk, int32_t K, int32_t V,
+                                                                   int32_t KP, double *kv)
+{
+    __shared__ double tile[32][33];
+    const int w0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int w = w0 + r, k = k0 + threadIdx.x;
+        tile[r][threadIdx.x] = (w < V && k < K) ? vk[(size_t)w * KP + k] : 0.0;
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int k = k0 + r, w = w0 + threadIdx.x;
+        if (k < K && w < V) kv[(size_t)k * V + w] = tile[threadIdx.x][r];
+    }
+}
+
 // opt_alpha (lda-alpha.c:42-68): Newton on log(alpha) from 100, one thread.
 // tail = [alpha_ss, likelihood, num_docs, visits].
 __global__ void alpha_newton_kernel(const double *tail, int32_t K, double *alpha)
