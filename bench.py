@@ -425,6 +425,8 @@ def _our_arm(args):
                      # ncu --set full, profiles/r1_estep_final.txt: dram read+write = 316 B per word visit
                      # (the phi row of every sweep streams through HBM); scaled to this launch's visits
                      "traffic": int(316.4 * visits / world), "traffic_source": "ncu dram__bytes per word visit x visits of this launch",
+                     # what the launch actually moves through HBM against the same peak (the phi rows of every sweep)
+                     "dram_frac": 316.4 * visits / world / (ms_estep * 1e-3) / 1e9 / peak,
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": int(alg_bytes), "ms_per_launch": ms_estep,
                      "fp64_pipe": "56 % busy (ncu sm__pipe_fp64_cycles_active), 256 FP64 of 492 instructions per warp word-visit",
@@ -557,6 +559,7 @@ def _score_arm(args):
         "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / args.steps * 1e3,
         "roofline": {"bound": "hbm", "kernel": "score_filter_paired_kernel<flow,10>", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": int(286.3 * n),
+                     "dram_frac": 286.3 * n / (statistics.mean(ms_score) * 1e-3) / 1e9 / peak,
                      "traffic_source": "ncu dram__bytes_read per event (profiles/r1_score.txt) x events",
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": n * (16 + 16 * K + 8), "ms_per_launch": statistics.mean(ms_score)},
