@@ -244,6 +244,21 @@ int oni_score_dns(int32_t device, int32_t num_topics, int32_t num_docs, int32_t 
                   const int32_t *doc, const int32_t *word, double tol, int64_t out_cap,
                   int64_t *out_idx, double *out_key, int64_t *out_n);
 
+/* The same two calls over several GPUs of this process (the Spark stage's events
+ * are independent): the events are cut into `ngpus` contiguous shares, devices 0..ngpus-1 each
+ * hold a copy of the two tables and filter and rank their share, and the host merges the ranked
+ * shares on (key, event index) -- the result is the single-GPU result, bit for bit.  No
+ * collective is involved. */
+int oni_score_flow_multi(int32_t ngpus, int32_t num_topics, int32_t num_docs, int32_t num_terms,
+                         const double *theta, const double *pwz, int64_t num_events,
+                         const int32_t *src_doc, const int32_t *dst_doc, const int32_t *src_word,
+                         const int32_t *dst_word, double tol, int64_t out_cap, int64_t *out_idx,
+                         double *out_key, double *out_src, double *out_dst, int64_t *out_n);
+int oni_score_dns_multi(int32_t ngpus, int32_t num_topics, int32_t num_docs, int32_t num_terms,
+                        const double *theta, const double *pwz, int64_t num_events,
+                        const int32_t *doc, const int32_t *word, double tol, int64_t out_cap,
+                        int64_t *out_idx, double *out_key, int64_t *out_n);
+
 /* The same path with the event indices already on the device (what the host  */
 /* entry points above are built on; a day of events is pushed chunk by chunk). */
 typedef struct oni_score_ctx oni_score_ctx;

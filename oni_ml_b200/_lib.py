@@ -100,6 +100,10 @@ SIGNATURES = {
                                  _i64, _vp, _vp, _vp, _vp, C.POINTER(_i64)]),
     "oni_score_dns": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, _i64, _vp, _vp, _f64, _i64, _vp,
                                 _vp, C.POINTER(_i64)]),
+    "oni_score_flow_multi": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _f64,
+                                 _i64, _vp, _vp, _vp, _vp, C.POINTER(_i64)]),
+    "oni_score_dns_multi": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, _i64, _vp, _vp, _f64, _i64, _vp,
+                                _vp, C.POINTER(_i64)]),
     "oni_score_create": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, C.POINTER(_vp)]),
     "oni_score_destroy": (None, [_vp]),
     "oni_score_begin": (C.c_int, [_vp]),

@@ -22,6 +22,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "common.h"
@@ -528,7 +530,8 @@ extern "C" int oni_score_get_stats(oni_score_ctx *c, double *ms_score, double *m
 static int score_host(int32_t device, int is_flow, int32_t K, int32_t D, int32_t V, const double *theta,
                       const double *pwz, int64_t n, const int32_t *a_doc, const int32_t *b_doc,
                       const int32_t *a_word, const int32_t *b_word, double tol, int64_t out_cap,
-                      int64_t *out_idx, double *out_key, double *out_a, double *out_b, int64_t *out_n)
+                      int64_t *out_idx, double *out_key, double *out_a, double *out_b, int64_t *out_n,
+                      int64_t base = 0 /* global index of this call's first event */)
 {
     if (n < 0 || out_cap < 0 || !theta || !pwz) return oni_set_error(ONI_ERR_ARG, "score: bad argument");
     oni_score_ctx *c = nullptr;
@@ -553,7 +556,7 @@ static int score_host(int32_t device, int is_flow, int32_t K, int32_t D, int32_t
             if (cudaMemcpyAsync(c->ev[q].p, src[q] + lo, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, c->stream) != cudaSuccess)
                 rc = oni_set_error(ONI_ERR_CUDA, "score: event upload failed");
         if (rc == ONI_OK)
-            rc = oni_score_events_device(c, is_flow, m, lo, (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p,
+            rc = oni_score_events_device(c, is_flow, m, base + lo, (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p,
                                          (int32_t *)c->ev[1].p, (int32_t *)c->ev[3].p, tol);
     }
     int64_t total = 0;
@@ -561,7 +564,7 @@ static int score_host(int32_t device, int is_flow, int32_t K, int32_t D, int32_t
     if (rc == ONI_OK) rc = oni_score_fetch(c, out_cap, out_idx, out_key);
     if (rc == ONI_OK && (out_a || out_b)) {
         if (chunk == n) {
-            rc = oni_score_fetch_sides(c, is_flow, out_cap, 0, (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p,
+            rc = oni_score_fetch_sides(c, is_flow, out_cap, base, (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p,
                                        (int32_t *)c->ev[1].p, (int32_t *)c->ev[3].p, out_a, out_b);
         } else {
             rc = oni_set_error(ONI_ERR_ARG, "score: per-side scores need the events in one chunk (n <= 2^28)");
@@ -591,6 +594,95 @@ extern "C" int oni_score_dns(int32_t device, int32_t K, int32_t D, int32_t V, co
     if (n > 0 && (!doc || !word)) return oni_set_error(ONI_ERR_ARG, "score_dns: null event array");
     return score_host(device, 0, K, D, V, theta, pwz, n, doc, nullptr, word, nullptr, tol, out_cap, out_idx,
                       out_key, nullptr, nullptr, out_n);
+}
+
+// Events split evenly over the GPUs of this process: tables replicated, every GPU
+// filters and ranks its own contiguous share, the host merges the ranked shares on (key, global
+// event index).  No collective: the shares meet only in the merge.
+static int score_multi(int32_t ngpus, int is_flow, int32_t K, int32_t D, int32_t V, const double *theta,
+                       const double *pwz, int64_t n, const int32_t *a_doc, const int32_t *b_doc,
+                       const int32_t *a_word, const int32_t *b_word, double tol, int64_t out_cap,
+                       int64_t *out_idx, double *out_key, double *out_a, double *out_b, int64_t *out_n)
+{
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return oni_set_error(ONI_ERR_CUDA, "no CUDA device: this engine has no CPU path");
+    if (ngpus < 1 || ngpus > ndev) return oni_set_error(ONI_ERR_ARG, "score: %d GPUs asked, %d visible", ngpus, ndev);
+    if (n < 0 || out_cap < 0) return oni_set_error(ONI_ERR_ARG, "score: bad argument");
+    struct Share {
+        int64_t lo = 0, n = 0, total = 0;
+        std::vector<int64_t> idx;
+        std::vector<double> key, a, b;
+        int rc = ONI_OK;
+        std::string msg;
+    };
+    std::vector<Share> sh(ngpus);
+    std::vector<std::thread> th;
+    const bool sides = out_a || out_b;
+    for (int g = 0; g < ngpus; g++) {
+        Share &s = sh[g];
+        s.lo = n * g / ngpus;
+        s.n = n * (g + 1) / ngpus - s.lo;
+        const size_t cap = (size_t)std::max<int64_t>(1, std::min(out_cap, s.n));
+        s.idx.resize(cap); s.key.resize(cap);
+        if (sides) { s.a.resize(cap); s.b.resize(cap); }
+        th.emplace_back([&, g] {
+            Share &me = sh[g];
+            me.rc = score_host(g, is_flow, K, D, V, theta, pwz, me.n, a_doc + me.lo, b_doc ? b_doc + me.lo : nullptr,
+                               a_word + me.lo, b_word ? b_word + me.lo : nullptr, tol, std::min(out_cap, me.n),
+                               me.idx.data(), me.key.data(), sides ? me.a.data() : nullptr,
+                               (sides && is_flow) ? me.b.data() : nullptr, &me.total, me.lo);
+            if (me.rc != ONI_OK) me.msg = oni_last_error();  // (the message is per thread)
+        });
+    }
+    for (auto &t : th) t.join();
+    int64_t total = 0;
+    for (int g = 0; g < ngpus; g++) {
+        if (sh[g].rc != ONI_OK) return oni_set_error(sh[g].rc, "GPU %d: %s", g, sh[g].msg.c_str());
+        total += sh[g].total;
+    }
+    // merge: ascending key, ties by global event index (each share is already in that order)
+    std::vector<int64_t> head(ngpus, 0), have(ngpus);
+    for (int g = 0; g < ngpus; g++) have[g] = std::min<int64_t>(sh[g].total, std::min(out_cap, sh[g].n));
+    const int64_t emit = std::min(out_cap, total);
+    for (int64_t r = 0; r < emit; r++) {
+        int best = -1;
+        for (int g = 0; g < ngpus; g++) {
+            if (head[g] >= have[g]) continue;
+            if (best < 0) { best = g; continue; }
+            const double kb = sh[best].key[head[best]], kg = sh[g].key[head[g]];
+            if (kg < kb || (kg == kb && sh[g].idx[head[g]] < sh[best].idx[head[best]])) best = g;
+        }
+        if (best < 0) break;
+        const int64_t h = head[best]++;
+        if (out_idx) out_idx[r] = sh[best].idx[h];
+        if (out_key) out_key[r] = sh[best].key[h];
+        if (out_a) out_a[r] = sh[best].a[h];
+        if (out_b && is_flow) out_b[r] = sh[best].b[h];
+    }
+    if (out_n) *out_n = total;
+    return ONI_OK;
+}
+
+extern "C" int oni_score_flow_multi(int32_t ngpus, int32_t K, int32_t D, int32_t V, const double *theta,
+                                    const double *pwz, int64_t n, const int32_t *src_doc, const int32_t *dst_doc,
+                                    const int32_t *src_word, const int32_t *dst_word, double tol, int64_t out_cap,
+                                    int64_t *out_idx, double *out_key, double *out_src, double *out_dst,
+                                    int64_t *out_n)
+{
+    if (!theta || !pwz || (n > 0 && (!src_doc || !dst_doc || !src_word || !dst_word)))
+        return oni_set_error(ONI_ERR_ARG, "score_flow_multi: null array");
+    return score_multi(ngpus, 1, K, D, V, theta, pwz, n, src_doc, dst_doc, src_word, dst_word, tol, out_cap, out_idx,
+                       out_key, out_src, out_dst, out_n);
+}
+
+extern "C" int oni_score_dns_multi(int32_t ngpus, int32_t K, int32_t D, int32_t V, const double *theta,
+                                   const double *pwz, int64_t n, const int32_t *doc, const int32_t *word, double tol,
+                                   int64_t out_cap, int64_t *out_idx, double *out_key, int64_t *out_n)
+{
+    if (!theta || !pwz || (n > 0 && (!doc || !word))) return oni_set_error(ONI_ERR_ARG, "score_dns_multi: null array");
+    return score_multi(ngpus, 0, K, D, V, theta, pwz, n, doc, nullptr, word, nullptr, tol, out_cap, out_idx, out_key,
+                       nullptr, nullptr, out_n);
 }
 
 // ------------------------------------------------------------------ lda_post.py

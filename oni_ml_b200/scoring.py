@@ -21,8 +21,9 @@ def _i32(a):
 
 
 def score_flow(theta, pwz, src_doc, dst_doc, src_word, dst_word, tol: float, out_cap: int | None = None,
-               device: int = 0, sides: bool = True) -> dict:
-    """oni_score_flow over host arrays.  theta [D][K], pwz [V][K]; index < 0 = miss."""
+               device: int = 0, sides: bool = True, ngpus: int = 0) -> dict:
+    """oni_score_flow over host arrays.  theta [D][K], pwz [V][K]; index < 0 = miss.
+    ngpus > 0: oni_score_flow_multi over devices 0..ngpus-1 (`device` is then ignored)."""
     L = _lib.load()
     theta, pwz = _f64(theta), _f64(pwz)
     sd, dd, sw, dw = map(_i32, (src_doc, dst_doc, src_word, dst_word))
@@ -32,9 +33,10 @@ def score_flow(theta, pwz, src_doc, dst_doc, src_word, dst_word, tol: float, out
     sa = np.zeros(max(cap, 1)) if sides else None
     sb = np.zeros(max(cap, 1)) if sides else None
     total = C.c_int64()
-    check(L.oni_score_flow(device, theta.shape[1], theta.shape[0], pwz.shape[0], ptr(theta), ptr(pwz),
-                           n, ptr(sd), ptr(dd), ptr(sw), ptr(dw), float(tol), cap, ptr(idx), ptr(key),
-                           ptr(sa), ptr(sb), C.byref(total)))
+    fn, first = (L.oni_score_flow_multi, ngpus) if ngpus > 0 else (L.oni_score_flow, device)
+    check(fn(first, theta.shape[1], theta.shape[0], pwz.shape[0], ptr(theta), ptr(pwz),
+             n, ptr(sd), ptr(dd), ptr(sw), ptr(dw), float(tol), cap, ptr(idx), ptr(key),
+             ptr(sa), ptr(sb), C.byref(total)))
     m = min(cap, total.value)
     out = dict(n=total.value, idx=idx[:m], key=key[:m])
     if sides:
@@ -42,7 +44,8 @@ def score_flow(theta, pwz, src_doc, dst_doc, src_word, dst_word, tol: float, out
     return out
 
 
-def score_dns(theta, pwz, doc, word, tol: float, out_cap: int | None = None, device: int = 0) -> dict:
+def score_dns(theta, pwz, doc, word, tol: float, out_cap: int | None = None, device: int = 0,
+              ngpus: int = 0) -> dict:
     L = _lib.load()
     theta, pwz = _f64(theta), _f64(pwz)
     d, w = _i32(doc), _i32(word)
@@ -50,8 +53,9 @@ def score_dns(theta, pwz, doc, word, tol: float, out_cap: int | None = None, dev
     cap = n if out_cap is None else int(out_cap)
     idx = np.zeros(max(cap, 1), dtype=np.int64); key = np.zeros(max(cap, 1))
     total = C.c_int64()
-    check(L.oni_score_dns(device, theta.shape[1], theta.shape[0], pwz.shape[0], ptr(theta), ptr(pwz), n,
-                          ptr(d), ptr(w), float(tol), cap, ptr(idx), ptr(key), C.byref(total)))
+    fn, first = (L.oni_score_dns_multi, ngpus) if ngpus > 0 else (L.oni_score_dns, device)
+    check(fn(first, theta.shape[1], theta.shape[0], pwz.shape[0], ptr(theta), ptr(pwz), n,
+             ptr(d), ptr(w), float(tol), cap, ptr(idx), ptr(key), C.byref(total)))
     m = min(cap, total.value)
     return dict(n=total.value, idx=idx[:m], key=key[:m])
 
