@@ -466,7 +466,8 @@ def fp64_roofline(visits_per_gpu, ms, clocks, sms):
 def score_arm(args):
     with QuietStdout():
         line = _score_arm(args)
-    emit(line)
+    if line is not None:
+        emit(line)
     return 0
 
 
@@ -474,12 +475,18 @@ def _score_arm(args):
     """BASELINE configs[4]: flow events scored from theta [1M x 20] / p(w|z) [50k x 20],
     threshold filter, ranked ascending.  One step = one pass over all events."""
     import torch
+    import torch.distributed as dist
     from oni_ml_b200 import scoring
     from oracle import pyoracle
-    dev = torch.device("cuda", 0)
-    torch.cuda.set_device(0)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
     D, V, K, n = WORKLOAD["docs_per_gpu"], WORKLOAD["vocab"], K_TOPICS, args.events
-    g = torch.Generator(device=dev); g.manual_seed(20160127)
+    g = torch.Generator(device=dev); g.manual_seed(20160127)  # the tables: the same on every rank
     th = torch._standard_gamma(torch.full((D, K), 0.3, dtype=torch.float64, device=dev), generator=g) + 1e-300
     th /= th.sum(1, keepdim=True)
     pw = torch._standard_gamma(torch.full((K, V), 0.05, dtype=torch.float64, device=dev), generator=g) + 1e-300
@@ -501,34 +508,80 @@ def _score_arm(args):
         a[torch.rand(n, generator=g, device=dev) < 1e-3] = -1  # lookup misses
         return a
     doc_skew = "zipf" if args.doc_dist == "zipf" else None  # uniform = worst-case locality
+    g.manual_seed(20160128 + rank)  # the events: every rank its own share (weak scaling), global index = rank*n + i
     ev = [draw(D, doc_skew), draw(D, doc_skew), draw(V, "cube"), draw(V, "cube")]
-    ctx = scoring.ScoreContext(theta, pwz, 0)
+    base = rank * n
+    ctx = scoring.ScoreContext(theta, pwz, local)
     # threshold at the 1e-3 quantile of a 2M-event sample (so the sort has ~n/1000 keys)
     m = min(n, 2_000_000)
     ctx.begin(); ctx.score_flow(*(a[:m] for a in ev), float("inf")); k = ctx.rank()
     _, keys = ctx.fetch(k)
     tol = float(keys[max(1, int(1e-3 * m))])
+    if world > 1:  # one threshold for the whole job: rank 0's
+        tt = torch.tensor([tol], dtype=torch.float64, device=dev)
+        dist.broadcast(tt, 0)
+        tol = float(tt[0])
     for _ in range(args.warmup):
-        ctx.begin(); ctx.score_flow(*ev, tol); ctx.rank()
+        ctx.begin(); ctx.score_flow(*ev, tol, idx_base=base); ctx.rank()
     torch.cuda.synchronize()
-    sampler = ClockSampler(0); sampler.start()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
     l0 = ctx.stats()["kernel_launches"]
     ms_score, ms_sort, t0 = [], [], time.perf_counter()
     for _ in range(args.steps):
-        ctx.begin(); ctx.score_flow(*ev, tol); surv = ctx.rank()
+        ctx.begin(); ctx.score_flow(*ev, tol, idx_base=base); surv = ctx.rank()
         st = ctx.stats(); ms_score.append(st["ms_score"]); ms_sort.append(st["ms_sort"])
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
-    clocks = sampler.stop()
+    clocks = sampler.stop() if sampler else None
     launches = ctx.stats()["kernel_launches"] - l0
     dev_ms = statistics.mean(ms_score) + statistics.mean(ms_sort)
     idx, key = ctx.fetch(min(surv, 1_000_000))
-    # e2e: host arrays through oni_score_flow (upload of 16 B/event inside)
+    surv_all, per_rank_ms = surv, [dev_ms]
+    if world > 1:
+        # device time of the step = the slowest rank's (CUDA events on each rank's stream)
+        tm = torch.tensor([dev_ms, float(launches), float(surv)], dtype=torch.float64, device=dev)
+        allr = [torch.zeros_like(tm) for _ in range(world)]
+        dist.all_gather(allr, tm)
+        per_rank_ms = [float(x[0]) for x in allr]
+        dev_ms = max(per_rank_ms)
+        launches = sum(int(x[1]) for x in allr)
+        surv_all = sum(int(x[2]) for x in allr)
+    # e2e: host arrays through oni_score_flow (upload of 16 B/event inside); with several ranks the
+    # ranked shares (at most 1M survivors each) are then gathered and merged on (key, global index)
     hev = [a.cpu().pin_memory().numpy() for a in ev]
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     t0 = time.perf_counter()
-    r = scoring.score_flow(theta, pwz, *hev, tol, out_cap=1_000_000, sides=False)
+    r = scoring.score_flow(theta, pwz, *hev, tol, out_cap=1_000_000, sides=False, device=local)
+    assert r["n"] == surv and np.array_equal(r["idx"] + base, idx)
+    if world > 1:
+        cap = 1_000_000
+        ki = torch.full((cap, 2), -1, dtype=torch.int64, device=dev)
+        m_own = len(r["idx"])
+        ki[:m_own, 0] = torch.from_numpy(r["key"].view(np.int64)).to(dev)
+        ki[:m_own, 1] = torch.from_numpy(r["idx"] + base).to(dev)
+        parts = [torch.empty_like(ki) for _ in range(world)]
+        dist.all_gather(parts, ki)
+        if rank == 0:
+            allk = torch.cat(parts).cpu().numpy()
+            allk = allk[allk[:, 1] >= 0]
+            order = np.lexsort((allk[:, 1], allk[:, 0].view(np.float64)))  # key, then global index
+            merged_idx = allk[order[:cap], 1]
+            assert len(merged_idx) == min(cap, surv_all) or surv_all > cap
+        dist.barrier()
     e2e_s = time.perf_counter() - t0
-    assert r["n"] == surv and np.array_equal(r["idx"], idx)
+    if world > 1:
+        te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_s = float(te[0])
+    if rank != 0:
+        dist.destroy_process_group()
+        return None
     # parity on a prefix against the oracle, and the CPU baseline from the same call
     mp = min(n, 10_000_000)
     L = pyoracle.lib()
@@ -543,19 +596,24 @@ def _score_arm(args):
                      and np.array_equal(pre["key"].view(np.int64), ok[:mm].view(np.int64)))
     peak, peak_src = peaks()
     achieved = n * (16 + 16 * K + 8) / (statistics.mean(ms_score) * 1e-3) / 1e9
+    if world > 1:
+        dist.destroy_process_group()
     return {
-        "metric": "flow_events_scored_per_sec", "value": n / (dev_ms * 1e-3), "unit": "events/s", "n_gpus": 1,
+        "metric": "flow_events_scored_per_sec", "value": world * n / (dev_ms * 1e-3), "unit": "events/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "post-LDA flow scoring (BASELINE configs[4] shape): %d events, theta %dx%d, p(w|z) %dx%d, "
                                "threshold at the 1e-3 score quantile (%d survivors ranked); one step = all events"
-                               % (n, D, K, V, K, surv) + ("; documents Zipf(1.0)" if args.doc_dist == "zipf" else
+                               % (world * n, D, K, V, K, surv_all) + ("; documents Zipf(1.0)" if args.doc_dist == "zipf" else
                                                           "; documents uniform (worst-case locality)"),
-                   "events": n, "threshold": tol, "doc_dist": args.doc_dist,
+                   "events": world * n, "events_per_gpu": n, "threshold": tol, "doc_dist": args.doc_dist,
+                   "parallelism": "events split over %d GPU(s), tables replicated, ranked shares merged on (key, index); no collective in the timed kernels" % world,
                    "l2": "event indices (16 B/event) and the 160 MB theta table exceed the L2"},
-        "e2e": {"value": n / e2e_s, "unit": "events/s", "h2d_bytes_per_step": 16 * n + theta.nbytes + pwz.nbytes,
+        "e2e": {"value": world * n / e2e_s, "unit": "events/s", "h2d_bytes_per_step": 16 * n + theta.nbytes + pwz.nbytes,
                 "d2h_bytes_per_step": 16 * min(surv, 1_000_000), "seconds": e2e_s,
-                "what": "oni_score_flow over host arrays (tables + event indices uploaded inside)"},
+                "what": "oni_score_flow over host arrays on every rank (tables + event indices uploaded inside)"
+                        + ("" if world == 1 else ", ranked shares gathered and merged on rank 0")},
+        "ms_per_rank": [round(x, 3) for x in per_rank_ms],
         "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / args.steps * 1e3,
         "roofline": {"bound": "hbm", "kernel": "score_filter_paired_kernel<flow,10>", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": int(286.3 * n),
