@@ -1,0 +1,49 @@
+"""Host-side corpus helpers (no GPU): the synthetic generator of SURVEY.md 8(d) and its
+shard mode, and the model.dat writer/reader round trip."""
+import os
+
+import numpy as np
+
+from oni_ml_b200.corpus import Corpus, read_model_dat, synth_corpus, write_model_dat
+
+
+def _word_mass(c):
+    return np.bincount(c.word, weights=c.count, minlength=c.num_terms)
+
+
+def test_shards_of_one_corpus_share_their_topics():
+    """bench.py gives rank r the seed base + r; with topic_seed = base the ranks draw different
+    documents from the SAME topics (rank 0's single stream draws those topics first), so a
+    multi-GPU step estimates one model of one corpus instead of a mixture of unrelated ones."""
+    base = 41
+    rank0 = synth_corpus(3000, 400, seed=base)
+    rank1 = synth_corpus(3000, 400, seed=base + 1, topic_seed=base)
+    alone = synth_corpus(3000, 400, seed=base + 1)
+    assert rank1.nnz != rank0.nnz and not np.array_equal(rank1.word[:50], rank0.word[:50])
+    assert np.corrcoef(_word_mass(rank0), _word_mass(rank1))[0, 1] > 0.95
+    assert abs(np.corrcoef(_word_mass(rank0), _word_mass(alone))[0, 1]) < 0.3
+    # the committed fixtures were generated without topic_seed: that stream must not move
+    again = synth_corpus(3000, 400, seed=base)
+    assert np.array_equal(again.word, rank0.word) and np.array_equal(again.count, rank0.count)
+
+
+def test_generator_shape_rules():
+    c = synth_corpus(2000, 300, mu=2.0, seed=5)
+    lens = np.diff(c.doc_ptr)
+    assert lens.min() >= 1 and lens.max() <= 300 and c.count.min() >= 1
+    assert set(np.unique(c.word)) == set(range(300))  # every word id occurs: num_terms = V
+    # a few documents repeat one word id (the flow quirk lda_pre.py keeps as separate pairs)
+    dup = sum(len(np.unique(c.word[a:b])) < b - a for a, b in zip(c.doc_ptr[:-1], c.doc_ptr[1:]))
+    assert dup > 0
+
+
+def test_model_dat_round_trip(tmp_path):
+    c = synth_corpus(300, 120, mu=1.5, seed=9)
+    p = os.path.join(tmp_path, "model.dat")
+    write_model_dat(p, c)
+    back = read_model_dat(p)
+    assert isinstance(back, Corpus) and back.num_terms == c.num_terms
+    assert np.array_equal(back.doc_ptr, c.doc_ptr) and np.array_equal(back.word, c.word)
+    assert np.array_equal(back.count, c.count)
+    first = open(p).readline().split()
+    assert int(first[0]) == len(first) - 1 and ":" in first[1]  # "N w:c w:c ..." (lda-data.c:35-51)
