@@ -369,6 +369,17 @@ int oni_flow_events_open(const char *flow_csv, const char *doc_results_csv,
 int oni_dns_events_open(const char *dns_csv, const char *top_domains_csv,
                         const char *doc_results_csv, const char *word_results_csv,
                         oni_events **out);
+/* The pre-LDA scripts also read the analysts' feedback (flow_pre_lda.scala:147-263 flow_scores.csv,
+ * dns_pre_lda.scala:70-138 dns_scores.csv): rows marked severity 3 are turned back into event
+ * rows (flow: every column the word does not use becomes "##") and appended dup_factor times
+ * each, behind the events of the day.  First line of the feedback file = header. */
+int oni_flow_events_open_feedback(const char *flow_csv, const char *feedback_csv, int32_t dup_factor,
+                                  const char *doc_results_csv, const char *word_results_csv,
+                                  oni_events **out);
+int oni_dns_events_open_feedback(const char *dns_csv, const char *top_domains_csv,
+                                 const char *feedback_csv, int32_t dup_factor,
+                                 const char *doc_results_csv, const char *word_results_csv,
+                                 oni_events **out);
 void oni_events_close(oni_events *ev);
 /* lines read, rows kept by the filters, distinct keys of the two result tables */
 int oni_events_info(const oni_events *ev, int64_t *lines_in, int64_t *rows, int32_t *num_docs,
@@ -388,7 +399,7 @@ int64_t oni_events_row_text(const oni_events *ev, int64_t row, char *buf, int64_
  * Flow writes the source-side list, then the destination-side list (a pair can occur in both,
  * as in the script).  Line order (Spark: hash partitioner) is first appearance here.  For this
  * stage the handle may be opened with doc_results_csv = word_results_csv = NULL.  The scripts'
- * optional analyst-feedback rows are not read: append them to the input file. */
+ * analyst-feedback rows come in through the *_open_feedback calls above. */
 int oni_events_word_counts(const oni_events *ev, const char *out_path, int64_t *num_lines);
 /* GPU: score every kept row, keep score < tol, rank ascending, write the rows to out_path */
 int oni_events_score_write(oni_events *ev, double tol, const char *out_path, int32_t device,

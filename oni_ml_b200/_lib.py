@@ -117,6 +117,9 @@ SIGNATURES = {
     "oni_lda_post_files": (C.c_int, [C.c_char_p, _i32]),
     "oni_flow_events_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(_vp)]),
     "oni_dns_events_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(_vp)]),
+    "oni_flow_events_open_feedback": (C.c_int, [C.c_char_p, C.c_char_p, _i32, C.c_char_p, C.c_char_p, C.POINTER(_vp)]),
+    "oni_dns_events_open_feedback": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, _i32, C.c_char_p, C.c_char_p,
+                                               C.POINTER(_vp)]),
     "oni_events_close": (None, [_vp]),
     "oni_events_info": (C.c_int, [_vp, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i32), C.POINTER(_i32)]),
     "oni_events_cuts": (C.c_int, [_vp, _i32, _vp, _i32, C.POINTER(_i32)]),

@@ -685,8 +685,74 @@ void dns_row_text(const oni_events &ev, size_t i, std::string &out)
     out += ','; out += w;
 }
 
+// Analyst feedback of the pre-LDA scripts: rows of the scores file that an analyst marked
+// severity 3 ("not a threat") are turned back into event rows and appended `dup` times each, so
+// that the next model finds them ordinary (flow_pre_lda.scala:147-263, dns_pre_lda.scala:70-138).
+bool parse_int_java(sv f, long *out)  // String.toInt: optional sign, digits, nothing else
+{
+    if (f.empty() || f.size() > 11) return false;
+    char buf[16];
+    memcpy(buf, f.data(), f.size());
+    buf[f.size()] = 0;
+    char *end = nullptr;
+    const long v = strtol(buf, &end, 10);
+    const bool starts = (buf[0] >= '0' && buf[0] <= '9') || ((buf[0] == '-' || buf[0] == '+') && buf[1] >= '0' && buf[1] <= '9');
+    if (!starts || end == buf || *end) return false;
+    *out = v;
+    return true;
+}
+
+int append_feedback(int kind, const char *path, int dup, std::string &data)
+{
+    if (dup < 0) return oni_set_error(ONI_ERR_ARG, "feedback: duplication factor %d", dup);
+    std::string text;
+    ONI_TRY(slurp(path, text));
+    std::vector<sv> lines, f, a, b;
+    split_lines(text, lines);
+    if (!data.empty() && data.back() != '\n') data += '\n';
+    std::string row;
+    for (size_t i = 1; i < lines.size(); i++) {  // (the first line is the header)
+        split_java(lines[i], ',', f);
+        long sev = 0;
+        row.clear();
+        if (kind) {
+            // flow_scores.csv: 22 columns; 0 severity, 1 start time "YYYY-MM-DD HH:MM:SS", 2/3 IPs,
+            // 4/5 ports, 8 packets, 9 bytes.  Every other column of the flow row becomes "##".
+            if (f.size() != 22) continue;
+            if (!parse_int_java(f[0], &sev)) return oni_set_error(ONI_ERR_IO, "%s line %zu: severity is not an integer", path, i + 1);
+            if (sev != 3) continue;
+            split_java(f[1], ' ', a);
+            if (a.size() < 2) return oni_set_error(ONI_ERR_IO, "%s line %zu: start time has no clock part", path, i + 1);
+            split_java(a[1], ':', b);
+            if (b.size() < 3) return oni_set_error(ONI_ERR_IO, "%s line %zu: clock part is not HH:MM:SS", path, i + 1);
+            for (int c = 0; c < 27; c++) {
+                sv v = "##";
+                if (c == 4) v = b[0]; else if (c == 5) v = b[1]; else if (c == 6) v = b[2];
+                else if (c == 8) v = f[2]; else if (c == 9) v = f[3]; else if (c == 10) v = f[4];
+                else if (c == 11) v = f[5]; else if (c == 16) v = f[8]; else if (c == 17) v = f[9];
+                if (c) row += ',';
+                row.append(v.data(), v.size());
+            }
+        } else {
+            // dns_scores.csv: 0 frame_time, 1 frame_len, 2 ip_dst, 3 name, 4 class, 5 type, 6 rcode,
+            // 18 severity, 23 unix_tstamp
+            if (f.size() < 24) return oni_set_error(ONI_ERR_IO, "%s line %zu: %zu columns, 24 expected", path, i + 1, f.size());
+            long flen = 0;
+            if (!parse_int_java(trim_java(f[1]), &flen) || !parse_int_java(trim_java(f[18]), &sev))
+                return oni_set_error(ONI_ERR_IO, "%s line %zu: frame_len / severity is not an integer", path, i + 1);
+            if (sev != 3) continue;
+            row.append(f[0].data(), f[0].size()); row += ',';
+            row.append(f[23].data(), f[23].size()); row += ',';
+            row += std::to_string(flen);
+            for (int c = 2; c <= 6; c++) { row += ','; row.append(f[c].data(), f[c].size()); }
+        }
+        for (int d = 0; d < dup; d++) { data += row; data += '\n'; }
+    }
+    return ONI_OK;
+}
+
 int open_common(int kind, const char *events_csv, const char *top_csv, const char *doc_results,
-                const char *word_results, oni_events **out)
+                const char *word_results, oni_events **out, const char *feedback_csv = nullptr, int dup = 0)
 {
     if (!events_csv || !out || (kind == 0 && !top_csv) || (!doc_results) != (!word_results))
         return oni_set_error(ONI_ERR_ARG, "events_open: null argument");
@@ -698,6 +764,7 @@ int open_common(int kind, const char *events_csv, const char *top_csv, const cha
     Laps laps;
     try {
         rc = slurp(events_csv, ev->data);
+        if (rc == ONI_OK && feedback_csv) rc = append_feedback(kind, feedback_csv, dup, ev->data);
         laps.lap("read events file");
         if (rc == ONI_OK && kind == 0) rc = slurp(top_csv, ev->top_text);
         ev->has_tables = doc_results != nullptr;  // absent for the pre-LDA word count
@@ -725,6 +792,22 @@ extern "C" int oni_dns_events_open(const char *dns_csv, const char *top_domains_
                                    const char *word_results_csv, oni_events **out)
 {
     return open_common(0, dns_csv, top_domains_csv, doc_results_csv, word_results_csv, out);
+}
+
+extern "C" int oni_flow_events_open_feedback(const char *flow_csv, const char *feedback_csv, int32_t dup_factor,
+                                             const char *doc_results_csv, const char *word_results_csv,
+                                             oni_events **out)
+{
+    if (!feedback_csv) return oni_set_error(ONI_ERR_ARG, "events_open_feedback: null feedback file");
+    return open_common(1, flow_csv, nullptr, doc_results_csv, word_results_csv, out, feedback_csv, dup_factor);
+}
+
+extern "C" int oni_dns_events_open_feedback(const char *dns_csv, const char *top_domains_csv, const char *feedback_csv,
+                                            int32_t dup_factor, const char *doc_results_csv,
+                                            const char *word_results_csv, oni_events **out)
+{
+    if (!feedback_csv) return oni_set_error(ONI_ERR_ARG, "events_open_feedback: null feedback file");
+    return open_common(0, dns_csv, top_domains_csv, doc_results_csv, word_results_csv, out, feedback_csv, dup_factor);
 }
 
 extern "C" void oni_events_close(oni_events *ev) { delete ev; }

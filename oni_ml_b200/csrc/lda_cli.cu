@@ -364,11 +364,16 @@ static int run_events(int flow, const char *events, const char *top, const char 
     return rc;
 }
 
-static int run_word_counts(int flow, const char *events, const char *top, const char *out_path)
+static int run_word_counts(int flow, const char *events, const char *top, const char *out_path,
+                           const char *feedback, int dup)
 {
     oni_events *ev = nullptr;
-    ONI_TRY(flow ? oni_flow_events_open(events, nullptr, nullptr, &ev)
-                 : oni_dns_events_open(events, top, nullptr, nullptr, &ev));
+    if (feedback)  // LPATH/<type>_scores.csv and DUPFACTOR of the scripts
+        ONI_TRY(flow ? oni_flow_events_open_feedback(events, feedback, dup, nullptr, nullptr, &ev)
+                     : oni_dns_events_open_feedback(events, top, feedback, dup, nullptr, nullptr, &ev));
+    else
+        ONI_TRY(flow ? oni_flow_events_open(events, nullptr, nullptr, &ev)
+                     : oni_dns_events_open(events, top, nullptr, nullptr, &ev));
     int64_t rows = 0, lines = 0;
     oni_events_info(ev, nullptr, &rows, nullptr, nullptr);
     const int rc = oni_events_word_counts(ev, out_path, &lines);
@@ -386,8 +391,10 @@ extern "C" int oni_lda_main(int argc, char **argv)
     if (argc > 2 && strcmp(argv[1], "post") == 0) return oni_lda_post_files(argv[2], 0);  // lda_post.py <dir>/
     // the Spark scoring stage (ml_ops.sh:108): <type>_post_lda.scala with FLOW_PATH / DNS_PATH, HPATH and TOL
     // the Spark word-count stage before lda_pre.py (ml_ops.sh:44-57): <type>_pre_lda.scala
-    if (argc > 3 && strcmp(argv[1], "flow_pre") == 0) return run_word_counts(1, argv[2], nullptr, argv[3]);
-    if (argc > 4 && strcmp(argv[1], "dns_pre") == 0) return run_word_counts(0, argv[2], argv[3], argv[4]);
+    if (argc > 3 && strcmp(argv[1], "flow_pre") == 0)
+        return run_word_counts(1, argv[2], nullptr, argv[3], argc > 5 ? argv[4] : nullptr, argc > 5 ? atoi(argv[5]) : 0);
+    if (argc > 4 && strcmp(argv[1], "dns_pre") == 0)
+        return run_word_counts(0, argv[2], argv[3], argv[4], argc > 6 ? argv[5] : nullptr, argc > 6 ? atoi(argv[6]) : 0);
     if (argc > 5 && strcmp(argv[1], "flow_post") == 0) return run_events(1, argv[2], nullptr, argv[3], argv[4], argv[5]);
     if (argc > 6 && strcmp(argv[1], "dns_post") == 0) return run_events(0, argv[2], argv[3], argv[4], argv[5], argv[6]);
     // lda-estimate.c:464-465
@@ -395,8 +402,8 @@ extern "C" int oni_lda_main(int argc, char **argv)
     printf("        lda inf [settings] [model] [data] [output filename]\n");
     printf("        lda pre [dir/]    (lda_pre.py: doc_wc.dat -> words.dat doc.dat model.dat)\n");
     printf("        lda post [dir/]   (lda_post.py: final.gamma final.beta -> doc_results.csv word_results.csv)\n");
-    printf("        lda flow_pre [flow.csv] [doc_wc.dat]                               (flow_pre_lda.scala)\n");
-    printf("        lda dns_pre [dns.csv] [top-1m.csv] [doc_wc.dat]                    (dns_pre_lda.scala)\n");
+    printf("        lda flow_pre [flow.csv] [doc_wc.dat] ([flow_scores.csv] [dupfactor])             (flow_pre_lda.scala)\n");
+    printf("        lda dns_pre [dns.csv] [top-1m.csv] [doc_wc.dat] ([dns_scores.csv] [dupfactor])   (dns_pre_lda.scala)\n");
     printf("        lda flow_post [flow.csv] [hpath/] [tol] [scored file]              (flow_post_lda.scala)\n");
     printf("        lda dns_post [dns.csv] [top-1m.csv] [hpath/] [tol] [scored file]   (dns_post_lda.scala)\n");
     return ONI_OK;

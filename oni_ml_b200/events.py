@@ -77,10 +77,16 @@ class FlowEvents(_Events):
     """oni_flow_events_open: flow_post_lda.scala up to the score loop."""
     _CUTS = ("time", "ibyt", "ipkt")
 
-    def __init__(self, flow_csv: str, doc_results_csv: str | None = None, word_results_csv: str | None = None):
+    def __init__(self, flow_csv: str, doc_results_csv: str | None = None, word_results_csv: str | None = None,
+                 feedback_csv: str | None = None, dup_factor: int = 0):
         super().__init__()
-        check(self._L.oni_flow_events_open(flow_csv.encode(), _enc(doc_results_csv), _enc(word_results_csv),
-                                           C.byref(self._h)))
+        if feedback_csv is None:
+            check(self._L.oni_flow_events_open(flow_csv.encode(), _enc(doc_results_csv), _enc(word_results_csv),
+                                               C.byref(self._h)))
+        else:
+            check(self._L.oni_flow_events_open_feedback(flow_csv.encode(), feedback_csv.encode(), dup_factor,
+                                                        _enc(doc_results_csv), _enc(word_results_csv),
+                                                        C.byref(self._h)))
 
     def indices(self):
         n = self.info()["rows"]
@@ -94,10 +100,15 @@ class DnsEvents(_Events):
     _CUTS = ("unix_tstamp", "frame_len", "subdomain_length", "subdomain_entropy", "num_periods")
 
     def __init__(self, dns_csv: str, top_domains_csv: str, doc_results_csv: str | None = None,
-                 word_results_csv: str | None = None):
+                 word_results_csv: str | None = None, feedback_csv: str | None = None, dup_factor: int = 0):
         super().__init__()
-        check(self._L.oni_dns_events_open(dns_csv.encode(), top_domains_csv.encode(), _enc(doc_results_csv),
-                                          _enc(word_results_csv), C.byref(self._h)))
+        if feedback_csv is None:
+            check(self._L.oni_dns_events_open(dns_csv.encode(), top_domains_csv.encode(), _enc(doc_results_csv),
+                                              _enc(word_results_csv), C.byref(self._h)))
+        else:
+            check(self._L.oni_dns_events_open_feedback(dns_csv.encode(), top_domains_csv.encode(),
+                                                       feedback_csv.encode(), dup_factor, _enc(doc_results_csv),
+                                                       _enc(word_results_csv), C.byref(self._h)))
 
     def indices(self):
         n = self.info()["rows"]

@@ -306,3 +306,36 @@ def dns_word_counts(dns_text, top_text):
         key = f[3] + " " + f[14]
         counts[key] = counts.get(key, 0) + 1
     return [k.split(" ")[0] + "," + k.split(" ")[1] + "," + str(c) for k, c in counts.items()]
+
+
+# ---------------------------------------------------------------- analyst feedback (pre-LDA scripts)
+def flow_feedback_rows(feedback_text, dup):
+    """flow_pre_lda.scala:147-263: severity-3 rows of flow_scores.csv as flow rows, dup times each."""
+    out = []
+    for line in text_lines(feedback_text)[1:]:
+        f = jsplit(line, ",")
+        if len(f) != 22 or int(f[0]) != 3:
+            continue
+        hms = jsplit(jsplit(f[1], " ")[1], ":")
+        row = ["##"] * 27
+        row[4], row[5], row[6] = hms[0], hms[1], hms[2]
+        row[8], row[9], row[10], row[11], row[16], row[17] = f[2], f[3], f[4], f[5], f[8], f[9]
+        out += [",".join(row)] * dup
+    return out
+
+
+def dns_feedback_rows(feedback_text, dup):
+    """dns_pre_lda.scala:70-138: severity-3 rows of dns_scores.csv as the eight selected columns."""
+    out = []
+    for line in text_lines(feedback_text)[1:]:
+        f = jsplit(line, ",")
+        if int(jtrim(f[18])) != 3:
+            continue
+        out += [",".join([f[0], f[23], str(int(jtrim(f[1]))), f[2], f[3], f[4], f[5], f[6]])] * dup
+    return out
+
+
+def with_rows(text, rows):
+    if text and not text.endswith("\n"):
+        text += "\n"
+    return text + "".join(r + "\n" for r in rows)

@@ -198,3 +198,52 @@ def test_word_counts_feed_lda_pre(tmp_path):
     r = subprocess.run([LDA_BIN, "dns_pre", dns, top, str(out)], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert out.read_text().split("\n")[:-1] == eo.dns_word_counts(open(dns).read(), open(top).read())
+
+
+def test_analyst_feedback_rows_join_the_word_counts(tmp_path):
+    """flow_scores.csv / dns_scores.csv rows of severity 3 come back as event rows, DUPFACTOR times
+    each, behind the events of the day (flow_pre_lda.scala:147-263, dns_pre_lda.scala:70-138)."""
+    rnd = random.Random(17)
+    flow, _, _ = events_data.make_flow(str(tmp_path), n=1500, seed=3)
+    fb = tmp_path / "flow_scores.csv"
+    lines = ["sev,tstart,srcIP,dstIP,sport,dport,proto,flag,ipkt,ibyt,lda_score,rank,a,b,c,d,e,f,g,h,i,j"]
+    for i in range(60):
+        sev = rnd.choice([0, 1, 2, 3, 3])
+        f = [str(sev), "2016-04-21 %02d:%02d:%02d" % (rnd.randint(0, 23), rnd.randint(0, 59), rnd.randint(0, 59)),
+             "10.9.%d.1" % i, "10.8.%d.2" % i, str(rnd.choice([80, 443, 0, 50000])), str(rnd.choice([22, 0, 60000])),
+             "TCP", ".A..", str(rnd.randint(1, 50)), str(rnd.randint(40, 90000)), "1e-9", str(i)] + ["x"] * 10
+        if i % 13 == 0:
+            f = f[:21]  # wrong column count: skipped
+        lines.append(",".join(f))
+    fb.write_text("\n".join(lines) + "\n")
+    out = tmp_path / "doc_wc.dat"
+    for dup in (0, 1, 3):
+        rows = eo.flow_feedback_rows(fb.read_text(), dup)
+        ref = eo.flow_word_counts(eo.with_rows(open(flow).read(), rows))
+        with FlowEvents(flow, feedback_csv=str(fb), dup_factor=dup) as ev:
+            assert ev.word_counts(str(out)) == len(ref)
+            assert ev.info()["rows"] == len(eo.flow_post(open(flow).read(), "", "", 0.0)["rows"]) + len(rows)
+        assert out.read_text().split("\n")[:-1] == ref
+    assert len(eo.flow_feedback_rows(fb.read_text(), 1)) > 10
+    bad = tmp_path / "bad.csv"
+    bad.write_text(lines[0] + "\n" + ",".join(["three"] + ["x"] * 21) + "\n")
+    with pytest.raises(_lib.OniError):
+        FlowEvents(flow, feedback_csv=str(bad), dup_factor=1)
+    # dns, through the command line
+    import subprocess
+    from oni_ml_b200 import LDA_BIN
+    dns, top, _, _ = events_data.make_dns(str(tmp_path), n=1500, seed=4)
+    fb2 = tmp_path / "dns_scores.csv"
+    hdr = ",".join("c%d" % i for i in range(24))
+    dl = [hdr]
+    for i in range(40):
+        f = ["Sep 13 2015 19:08:0%d UTC" % (i % 10), " %d " % rnd.choice([60, 74, 300]), "172.16.9.%d" % i,
+             rnd.choice(events_data.DNS_NAMES[:6]), "0x00000001", "1", "0"] + ["y"] * 11 + [" %d" % rnd.choice([1, 3, 3]), "", "", "", "",
+             str(1442171291 + i)]
+        dl.append(",".join(f))
+    fb2.write_text("\n".join(dl) + "\n")
+    r = subprocess.run([LDA_BIN, "dns_pre", dns, top, str(out), str(fb2), "2"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    rows = eo.dns_feedback_rows(fb2.read_text(), 2)
+    assert len(rows) > 20
+    assert out.read_text().split("\n")[:-1] == eo.dns_word_counts(eo.with_rows(open(dns).read(), rows), open(top).read())
