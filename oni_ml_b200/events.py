@@ -115,3 +115,31 @@ class DnsEvents(_Events):
         d, w = np.zeros(max(n, 1), dtype=np.int32), np.zeros(max(n, 1), dtype=np.int32)
         check(self._L.oni_events_indices(self._h, ptr(d), None, ptr(w), None))
         return d[:n], w[:n]
+
+
+DNS_COLUMNS = ("frame_time", "unix_tstamp", "frame_len", "ip_dst", "dns_qry_name", "dns_qry_class", "dns_qry_type",
+               "dns_qry_rcode")
+
+
+def dns_parquet_to_csv(file_list: str, out_csv: str, as_reference: bool = True) -> int:
+    """The parquet front end of dns_pre_lda.scala:140-152 / dns_post_lda.scala:108-121: DNS_PATH is a
+    comma-separated list of parquet files; rows with a null frame_len or unix_tstamp are dropped, the
+    eight columns the scripts select are joined with ',' (Row.mkString: null prints as "null"), one
+    line per event, ready for oni_dns_events_open.  `as_reference` keeps the scripts' loop condition
+    `index > 1`, which never reads the SECOND file of the list; pass False to read every file.
+    Host-side glue with no arithmetic; needs pyarrow.  Returns the number of lines written."""
+    import pyarrow.parquet as pq
+
+    files = file_list.split(",")
+    use = [f for i, f in enumerate(files) if i == 0 or i > 1 or not as_reference]
+    n = 0
+    with open(out_csv, "w") as out:
+        for path in use:
+            t = pq.read_table(path, columns=list(DNS_COLUMNS))
+            cols = [t.column(c).to_pylist() for c in DNS_COLUMNS]
+            for row in zip(*cols):
+                if row[2] is None or row[1] is None:
+                    continue
+                out.write(",".join("null" if v is None else str(v) for v in row) + "\n")
+                n += 1
+    return n

@@ -247,3 +247,27 @@ def test_analyst_feedback_rows_join_the_word_counts(tmp_path):
     rows = eo.dns_feedback_rows(fb2.read_text(), 2)
     assert len(rows) > 20
     assert out.read_text().split("\n")[:-1] == eo.dns_word_counts(eo.with_rows(open(dns).read(), rows), open(top).read())
+
+
+def test_dns_parquet_front_end(tmp_path):
+    """DNS_PATH as the scripts take it: parquet files, null filter, eight columns, and the scripts'
+    own habit of skipping the second file of the list (dns_pre_lda.scala:143-147)."""
+    pa = pytest.importorskip("pyarrow")
+    import pyarrow.parquet as pq
+    from oni_ml_b200.events import DNS_COLUMNS, dns_parquet_to_csv
+    paths = []
+    for k in range(3):
+        t = pa.table({
+            "frame_time": ["t%d_%d" % (k, i) for i in range(4)], "unix_tstamp": [1442171291 + i if i != 1 else None for i in range(4)],
+            "frame_len": [60 + i if i != 2 else None for i in range(4)], "ip_dst": ["10.0.%d.%d" % (k, i) for i in range(4)],
+            "dns_qry_name": ["a.b.com", None, "c.org", "d.net"], "dns_qry_class": ["0x1"] * 4, "dns_qry_type": [1, 28, 1, 15],
+            "dns_qry_rcode": [0, 0, 3, 0], "unused": [1.5] * 4})
+        p = str(tmp_path / ("f%d.parquet" % k))
+        pq.write_table(t, p)
+        paths.append(p)
+    out = str(tmp_path / "dns.csv")
+    assert dns_parquet_to_csv(",".join(paths), out) == 4  # files 0 and 2, two rows each survive the null filter
+    lines = open(out).read().split("\n")[:-1]
+    assert lines[0] == "t0_0,1442171291,60,10.0.0.0,a.b.com,0x1,1,0" and lines[1].startswith("t0_3,1442171294,63,")
+    assert all(ln.startswith(("t0_", "t2_")) for ln in lines) and len(lines[0].split(",")) == len(DNS_COLUMNS)
+    assert dns_parquet_to_csv(",".join(paths), out, as_reference=False) == 6
