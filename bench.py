@@ -429,9 +429,9 @@ def _our_arm(args):
                      "dram_frac": 316.4 * visits / world / (ms_estep * 1e-3) / 1e9 / peak,
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": int(alg_bytes), "ms_per_launch": ms_estep,
-                     "fp64_pipe": "56 % busy (ncu sm__pipe_fp64_cycles_active), 256 FP64 of 492 instructions per warp word-visit",
+                     "fp64_pipe": "56 % busy (ncu sm__pipe_fp64_cycles_active), 240 FP64 of 474 instructions per warp word-visit",
                      # the limiter, measured live: FP64 lane-operations of the visit body (SASS count:
-                     # 147 DFMA + 56 DMUL + 53 DADD per warp visit of 8 documents = 1024 per word visit)
+                     # 141 DFMA + 51 DMUL + 48 DADD per warp visit of 8 documents = 960 per word visit)
                      # x this launch's visits / launch time, against SMs x 64 FP64 lanes x the SM clock
                      # sampled during the timed region
                      "fp64": fp64_roofline(visits / world, ms_estep, clocks, torch.cuda.get_device_properties(dev).multi_processor_count) if K_TOPICS == 20 else None,
@@ -453,12 +453,12 @@ def _our_arm(args):
 
 
 def fp64_roofline(visits_per_gpu, ms, clocks, sms):
-    lane_ops = 1024.0 * visits_per_gpu
+    lane_ops = 960.0 * visits_per_gpu
     achieved = lane_ops / (ms * 1e-3) / 1e9
     mhz = (clocks or {}).get("sm_mhz") or 0
     peak = sms * 64 * mhz * 1e6 / 1e9 if mhz else None
     return {"achieved": achieved, "peak": peak, "unit": "G fp64 lane-ops/s (an FMA counts once)",
-            "frac": (achieved / peak) if peak else None, "lane_ops_per_word_visit": 1024,
+            "frac": (achieved / peak) if peak else None, "lane_ops_per_word_visit": 960,
             "peak_source": "%d SMs x 64 FP64 lanes x %.0f MHz (median SM clock under load)" % (sms, mhz)}
 
 
