@@ -12,6 +12,14 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    # The tests exercise the built library, the `lda` executable and the compiled oracle.  They are
+    # built artefacts (not in git): a checkout that has not run __graft_entry__.build() yet gets them
+    # here.  Nothing is rebuilt when they exist.
+    need = [os.path.join(ROOT, "oni_ml_b200", "liboni_lda.so"), os.path.join(ROOT, "oni_ml_b200", "bin", "lda"),
+            os.path.join(ROOT, "oracle", "_build", "liboni_oracle.so")]
+    if not all(os.path.exists(p) for p in need):
+        import __graft_entry__
+        __graft_entry__.build()
 
 
 @pytest.fixture(scope="session")
