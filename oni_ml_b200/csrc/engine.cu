@@ -31,6 +31,7 @@
 #include "corpus_index.cuh"
 #include "estep_launch.h"
 #include "mt19937.h"
+#include "psi_table.h"
 #include "radix_sort.cuh"
 #include "suffstats.cuh"
 
@@ -123,6 +124,8 @@ struct oni_lda_ctx {
     double *d_phi = nullptr, *d_gamma = nullptr, *d_doc_lik = nullptr, *d_doc_ass = nullptr;
     int32_t *d_doc_iters = nullptr;
     double *d_ss = nullptr, *d_partial = nullptr, *d_block_partial = nullptr;
+    double *d_long_tabs = nullptr;  // psi_table.h: [PSI_N*6] psi coefficients, then [EXK_N] 2^(i/2048)
+    bool long_kernel = false;       // long documents go to estep_long_kernel (K <= 128)
     unsigned int *d_ticket = nullptr, *d_done = nullptr;
     int32_t *d_nan = nullptr;
     double *h_pinned = nullptr;  // [8] tail + alpha + nan flag readback
@@ -440,6 +443,18 @@ static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_setti
         c->T_long = (K + c->G_long - 1) / c->G_long;
         if (c->T_long > 8) { c->G_long = 32; c->T_long = (K + 31) / 32; }
     }
+    if (G < 32 && c->G_long == 32 && K <= 128) {
+        // the short-chain kernel for long documents and its tables (ONI_LDA_LONG_KERNEL=0: the
+        // one-document-per-warp build of estep_kernel instead, for A/B runs)
+        const char *env = getenv("ONI_LDA_LONG_KERNEL");
+        c->long_kernel = !(env && atoi(env) == 0);
+    }
+    if (c->long_kernel) {
+        std::vector<double> tabs((size_t)PSI_N * PSI_COEF + EXK_N);
+        build_long_tables(tabs.data(), tabs.data() + (size_t)PSI_N * PSI_COEF);
+        ONI_TRY(dev_alloc(&c->d_long_tabs, tabs.size()));
+        ONI_CUDA(cudaMemcpy(c->d_long_tabs, tabs.data(), sizeof(double) * tabs.size(), cudaMemcpyHostToDevice));
+    }
     ONI_TRY(dev_alloc(&c->d_logbeta_t, (size_t)V * c->KP));
     ONI_TRY(dev_alloc(&c->d_alpha, 1));
     ONI_TRY(dev_alloc(&c->d_ss, c->ss_count()));
@@ -461,7 +476,7 @@ extern "C" void oni_lda_destroy(oni_lda_ctx *c)
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     free_corpus(c);
     cudaFree(c->d_logbeta_t); cudaFree(c->d_alpha); cudaFree(c->d_ss); cudaFree(c->d_block_partial);
-    cudaFree(c->d_ticket); cudaFree(c->d_done); cudaFree(c->d_nan);
+    cudaFree(c->d_ticket); cudaFree(c->d_done); cudaFree(c->d_nan); cudaFree(c->d_long_tabs);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto &e : c->ev) if (e) cudaEventDestroy(e);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -604,6 +619,8 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
     p.D = c->D; p.K = c->K; p.KP = c->KP;
     p.var_max_iter = c->var_max_iter;
     p.var_converged = (double)c->st.var_converged;  // float promoted, lda-inference.c:46
+    p.psi_tab = c->d_long_tabs;
+    p.exk_tab = c->d_long_tabs ? c->d_long_tabs + (size_t)PSI_N * PSI_COEF : nullptr;
 
     // exp(x) cannot underflow for every topic of a word unless digamma(alpha)
     // is hugely negative, i.e. alpha tiny; then use the max-shifted kernel.
@@ -618,8 +635,10 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         EstepParams px = p;
         px.D = c->n_excl;
         px.ticket = c->d_ticket + 2;
-        cudaError_t e = launch_estep(c->G_long, c->T_long, shift, px, c->sm_count, c->stream_excl, /*longdoc=*/true,
-                                     /*exclusive_blocks=*/(c->n_excl + 3) / 4);
+        cudaError_t e = (c->long_kernel && !shift)
+            ? launch_estep_long(c->K, px, c->sm_count, c->stream_excl, /*exclusive_blocks=*/(c->n_excl + 3) / 4)
+            : launch_estep(c->G_long, c->T_long, shift, px, c->sm_count, c->stream_excl, /*longdoc=*/true,
+                           /*exclusive_blocks=*/(c->n_excl + 3) / 4);
         if (e != cudaSuccess)
             return oni_set_error(ONI_ERR_CUDA, "E-step launch (exclusive, T=%d): %s", c->T_long, cudaGetErrorString(e));
         c->launches++;
@@ -634,7 +653,9 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         pl.order = c->d_order + c->n_excl;
         pl.D = c->n_long - c->n_excl;
         pl.ticket = c->d_ticket + 1;
-        cudaError_t e = launch_estep(c->G_long, c->T_long, shift, pl, c->sm_count, c->stream_long, /*longdoc=*/true);
+        cudaError_t e = (c->long_kernel && !shift)
+            ? launch_estep_long(c->K, pl, c->sm_count, c->stream_long)
+            : launch_estep(c->G_long, c->T_long, shift, pl, c->sm_count, c->stream_long, /*longdoc=*/true);
         if (e != cudaSuccess)
             return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=%d,T=%d): %s", c->G_long, c->T_long, cudaGetErrorString(e));
         c->launches++;

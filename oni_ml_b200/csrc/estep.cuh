@@ -113,6 +113,8 @@ struct EstepParams {
     int32_t D, K, KP;
     int32_t var_max_iter;      // -1 = no cap
     double var_converged;
+    const double *psi_tab;     // long-document kernel only (psi_table.h): [PSI_N][6]
+    const double *exk_tab;     // ... [EXK_N]
 };
 
 __device__ __forceinline__ void prefetch_l2(const void *p)

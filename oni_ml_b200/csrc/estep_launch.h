@@ -18,6 +18,11 @@ namespace oni {
 cudaError_t launch_estep(int G, int T, bool shift, const EstepParams &p, int sm_count,
                          cudaStream_t stream, bool longdoc = false, int exclusive_blocks = 0);
 
+// The short-chain long-document kernel (estep_long.cuh): one document per warp, K <= 128, no
+// max-shift.  exclusive_blocks as above; otherwise one block of 4 documents per SM at most.
+cudaError_t launch_estep_long(int K, const EstepParams &p, int sm_count, cudaStream_t stream,
+                              int exclusive_blocks = 0);
+
 cudaError_t launch_estep_g1(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 cudaError_t launch_estep_g2(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);
 cudaError_t launch_estep_g4(int T, bool shift, const EstepParams &p, int sm_count, cudaStream_t s);

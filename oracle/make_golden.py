@@ -80,6 +80,35 @@ def make_c1():
                                                    int(c.count.astype(np.int64).sum()), int(c.doc_ptr.sum())))
 
 
+def make_c2(nproc=None):
+    """BASELINE.json configs[1], the size the headline is quoted on: 1M documents, 50k words,
+    K=20, shipped settings, `est 2.5 20 ... random` (ml_ops.sh:80) on the reference binary with
+    `nproc` forked ranks (lda-estimate.c:201 deals documents d = myid, myid+nproc, ...).  Takes
+    the better part of an hour on 8 cores, so it is not part of main(): run
+    `python oracle/make_golden.py c2`.  Kept: likelihood.dat, final.other, 000.other, every
+    5000th row of final.gamma, every 250th column of final.beta, and a CRC of the corpus the
+    tests regenerate from its seed (CPU generator: the same stream on every machine)."""
+    nproc = nproc or max(1, (os.cpu_count() or 2) - 1)
+    c = synth_corpus(1_000_000, 50_000, k_true=20, mu=3.5, seed=20160123)
+    out = os.path.join(GOLD, "c2_flow_day")
+    with tempfile.TemporaryDirectory() as tmp:
+        model = os.path.join(tmp, "model.dat")
+        write_model_dat(model, c)
+        run_ref(model, SETTINGS_SHIPPED, "2.5", 20, 4357, nproc,
+                ["000.other", "likelihood.dat", "final.other", "final.gamma", "final.beta"], out)
+    gam = np.loadtxt(os.path.join(out, "final.gamma"))
+    beta = np.loadtxt(os.path.join(out, "final.beta"))
+    np.savetxt(os.path.join(out, "final.gamma.rows5000"), gam[::5000], fmt="%.10f")
+    np.savetxt(os.path.join(out, "final.beta.cols250"), beta[:, ::250], fmt="%.10f")
+    os.remove(os.path.join(out, "final.gamma"))
+    os.remove(os.path.join(out, "final.beta"))
+    with open(os.path.join(out, "corpus.txt"), "w") as f:
+        f.write("synth_corpus(1000000, 50000, k_true=20, mu=3.5, seed=20160123): %d docs %d pairs %d tokens\n"
+                % (c.num_docs, c.nnz, c.tokens))
+        f.write("crc word %d count %d ptr %d\n" % (int(c.word.astype(np.int64).sum()),
+                                                   int(c.count.astype(np.int64).sum()), int(c.doc_ptr.sum())))
+
+
 def make_pre():
     """lda_pre.py fixture: a doc_wc.dat shaped like flow_pre_lda.scala's output (ip,word,count;
     words repeat inside a document, one field is quoted) and what the REFERENCE script
@@ -148,4 +177,7 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "c2":
+        make_c2(int(sys.argv[2]) if len(sys.argv) > 2 else None)
+    else:
+        main()

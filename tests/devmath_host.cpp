@@ -6,6 +6,8 @@
 #include <stdlib.h>
 
 #include "../oni_ml_b200/csrc/devmath.cuh"
+#include "../oni_ml_b200/csrc/psi_table.h"
+#include <vector>
 
 static const oni::MathTables T = ONI_MATH_TABLES_INIT;
 
@@ -65,6 +67,41 @@ int main(void)
         if (d / scale > worst_lg) worst_lg = d / scale;
     }
     printf("lgamma_max_rel %.3e\n", worst_lg);
+    // the long-document kernel's tables (psi_table.h): digamma by interval polynomial, short-chain exp
+    {
+        std::vector<double> psi((size_t)oni::PSI_N * oni::PSI_COEF), exk(oni::EXK_N);
+        oni::build_long_tables(psi.data(), exk.data());
+        double worst_psi = 0, worst_expk = 0;
+        int index_ok = oni::psi_index(ldexp(1.0, oni::PSI_EXP_LO)) == 0 &&
+                       oni::psi_index(nextafter(ldexp(1.0, oni::PSI_EXP_HI), 0.0)) == oni::PSI_N - 1 &&
+                       (unsigned)oni::psi_index(nextafter(ldexp(1.0, oni::PSI_EXP_LO), 0.0)) >= (unsigned)oni::PSI_N &&
+                       oni::psi_index(ldexp(1.0, oni::PSI_EXP_HI)) >= oni::PSI_N &&
+                       (unsigned)oni::psi_index(NAN) >= (unsigned)oni::PSI_N && (unsigned)oni::psi_index(-1.0) >= (unsigned)oni::PSI_N &&
+                       (unsigned)oni::psi_index(0.0) >= (unsigned)oni::PSI_N && (unsigned)oni::psi_index(INFINITY) >= (unsigned)oni::PSI_N;
+        for (int i = 0; i < 4000000; i++) {
+            double g = ldexp(1.0 + urand(), oni::PSI_EXP_LO + (int)(urand() * (oni::PSI_EXP_HI - oni::PSI_EXP_LO)));
+            if (i % 5 == 0) {  // interval edges
+                const int idx = (int)(urand() * oni::PSI_N);
+                g = ldexp(1.0 + (double)(idx & 63) / 64.0, oni::PSI_EXP_LO + (idx >> 6));
+                if (i % 10 == 0) g = nextafter(g, 0.0);
+                if (g < ldexp(1.0, oni::PSI_EXP_LO)) g = ldexp(1.0, oni::PSI_EXP_LO);
+            }
+            const int idx = oni::psi_index(g);
+            if (idx < 0 || idx >= oni::PSI_N) { index_ok = 0; continue; }
+            const long double want = oni::psi_ref_ld((long double)g);
+            const double got = oni::psi_poly(g, &psi[(size_t)idx * oni::PSI_COEF], 0.0);
+            const double d = fabs((double)((long double)got - want)) / fmax(fabsl(want), 1.0L);
+            if (d > worst_psi) worst_psi = d;
+            double x = -700.0 + 1400.0 * urand();
+            if (i & 1) x = -40.0 + 60.0 * urand();
+            double e = ulp_err(oni::exp_k(x, exk.data()), expl((long double)x)) - 0.6 * fabs(x);
+            if (e > worst_expk) worst_expk = e;
+        }
+        int edge = oni::exp_k(-5e5, exk.data()) < 1e-300 && oni::exp_k(-5e5, exk.data()) > 0 &&
+                   fabs(oni::exp_k(0.0, exk.data()) - 1.0) < 5e-16;
+        printf("psi_table_max_rel %.3e\nexpk_max_ulp_beyond_model %.3f\npsi_index_ok %d\nexpk_edge_ok %d\n",
+               worst_psi, worst_expk, index_ok, edge);
+    }
     // flush and edge behaviour
     int edge_ok = oni::exp_tab(-708.5, T.ex) < 1e-306 && oni::exp_tab(-1e6, T.ex) < 1e-306 && oni::exp_tab(-1e6, T.ex) > 0 &&
                   fabs(oni::exp_tab(0.0, T.ex) - 1.0) < 5e-16 && fabs(oni::log_tab(1.0, T.lg)) < 1e-16;

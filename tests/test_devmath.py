@@ -20,6 +20,10 @@ def test_devmath_accuracy_on_host(tmp_path):
     assert float(vals["digamma_max_rel"]) < 4e-15
     assert float(vals["lgamma_max_rel"]) < 4e-15
     assert vals["edge_ok"] == "1"
+    # psi_table.h (long-document kernel): the tabulated reference digamma and the short-chain exp
+    assert float(vals["psi_table_max_rel"]) < 1e-14  # relative to max(1, |psi|)
+    assert float(vals["expk_max_ulp_beyond_model"]) < 3.0  # ulp in excess of 0.6 ulp per unit of |x|
+    assert vals["psi_index_ok"] == "1" and vals["expk_edge_ok"] == "1"
 
 
 def test_generated_tables_are_current(tmp_path):
