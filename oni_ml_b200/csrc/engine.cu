@@ -37,6 +37,8 @@
 
 using namespace oni;
 
+static const MathTables g_host_tables = ONI_MATH_TABLES_INIT;  // host copy (digamma_ref on the host)
+
 // ----------------------------------------------------------------- NCCL, lazily
 // The library must load on hosts without NCCL (single-GPU use), so the few
 // entry points are resolved with dlopen on first use.
@@ -126,6 +128,11 @@ struct oni_lda_ctx {
     double *d_ss = nullptr, *d_partial = nullptr, *d_block_partial = nullptr;
     double *d_long_tabs = nullptr;  // psi_table.h: [PSI_N*6] psi coefficients, then [EXK_N] 2^(i/2048)
     bool long_kernel = false;       // long documents go to estep_long_kernel (K <= 128)
+    // What the unshifted kernels need to know about a model that came from outside (set_model,
+    // `lda inf`, a model-root start): the smallest entry, and the smallest per-word maximum over
+    // topics.  Models written by the M-step never go below the -100 floor (lda-model.c:42).
+    double model_min = -100.0, model_min_rowmax = -100.0;
+    int64_t max_doc_pairs = 0;
     unsigned int *d_ticket = nullptr, *d_done = nullptr;
     int32_t *d_nan = nullptr;
     double *h_pinned = nullptr;  // [8] tail + alpha + nan flag readback
@@ -214,6 +221,8 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     int32_t n_long = 0;
     if (c->long_min > 0)
         for (int32_t d = 0; d < D; d++) n_long += (h_ptr[d + 1] - h_ptr[d]) >= c->long_min;
+    int64_t max_pairs = 0;
+    for (int32_t d = 0; d < D; d++) max_pairs = std::max<int64_t>(max_pairs, h_ptr[d + 1] - h_ptr[d]);
     // A document long enough for its serial chain of word visits to outlast the rest of the
     // E-step sets the pace of the whole launch, and twice over when its warp shares a scheduler
     // with busy warps.  The few longest documents therefore get SMs to themselves.  Default
@@ -230,7 +239,7 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     tm.lap("validate doc_ptr");
 
     free_corpus(c);
-    c->D = D; c->nnz = nnz; c->n_long = n_long; c->n_excl = n_excl;
+    c->D = D; c->nnz = nnz; c->n_long = n_long; c->n_excl = n_excl; c->max_doc_pairs = max_pairs;
     cudaStream_t s = c->stream;
     ONI_TRY(dev_alloc(&c->d_tok, (size_t)nnz));
     ONI_TRY(dev_alloc(&c->d_doc_ptr, (size_t)D + 1));
@@ -536,6 +545,25 @@ static int upload_model(oni_lda_ctx *c, const double *logbeta, double alpha)
 {
     // the [K][V] -> [V][KP] layout change happens on the device (a strided host loop over K*V
     // doubles took 100 ms at K = 50, V = 200k)
+    {
+        // exp(digamma(gamma) + log beta) must be a normal number for at least one topic of every
+        // word, or the unshifted E-step normalises garbage (the reference's log_sum chain,
+        // lda-inference.c:53-64, has no such limit): remember how low this model goes
+        const size_t V = (size_t)c->V;
+        std::vector<double> rowmax(V, -INFINITY);
+        double lo = INFINITY;
+        for (int k = 0; k < c->K; k++) {
+            const double *row = logbeta + (size_t)k * V;
+            for (size_t w = 0; w < V; w++) {
+                const double x = row[w];
+                if (x != x) return oni_set_error(ONI_ERR_ARG, "model: log beta[%d][%zu] is NaN", k, w);
+                rowmax[w] = x > rowmax[w] ? x : rowmax[w];
+                lo = x < lo ? x : lo;
+            }
+        }
+        c->model_min = lo;
+        c->model_min_rowmax = *std::min_element(rowmax.begin(), rowmax.end());
+    }
     double *stage = nullptr;
     ONI_TRY(dev_alloc(&stage, (size_t)c->K * c->V));
     cudaError_t e = cudaMemcpyAsync(stage, logbeta, sizeof(double) * (size_t)c->K * c->V, cudaMemcpyHostToDevice, c->stream);
@@ -622,9 +650,15 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
     p.psi_tab = c->d_long_tabs;
     p.exk_tab = c->d_long_tabs ? c->d_long_tabs + (size_t)PSI_N * PSI_COEF : nullptr;
 
-    // exp(x) cannot underflow for every topic of a word unless digamma(alpha)
-    // is hugely negative, i.e. alpha tiny; then use the max-shifted kernel.
-    const bool shift = !(c->alpha > 0.01);
+    // exp(x) cannot underflow for every topic of a word unless digamma(alpha) is hugely
+    // negative (alpha tiny) or the model itself is (a loaded model may hold a word whose every
+    // topic sits below -600); then use the max-shifted kernel.  gamma >= alpha, so
+    // digamma(alpha) + the smallest per-word maximum bounds the best exponent of any visit.
+    const bool shift = !(c->alpha > 0.01) ||
+                       !(digamma_ref(c->alpha, g_host_tables.lg) + c->model_min_rowmax > -600.0);
+    // the short-chain kernel's exp takes arguments down to -7e5 and its offsets are 32-bit
+    const bool use_long = c->long_kernel && !shift && c->model_min > -1.0e5 &&
+                          (double)c->max_doc_pairs * c->KP < 4.0e9;
 
     ONI_CUDA(cudaMemsetAsync(c->d_ticket, 0, 3 * sizeof(unsigned), s));
     ONI_CUDA(cudaEventRecord(c->ev[0], s));
@@ -635,7 +669,7 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         EstepParams px = p;
         px.D = c->n_excl;
         px.ticket = c->d_ticket + 2;
-        cudaError_t e = (c->long_kernel && !shift)
+        cudaError_t e = use_long
             ? launch_estep_long(c->K, px, c->sm_count, c->stream_excl, /*exclusive_blocks=*/(c->n_excl + 3) / 4)
             : launch_estep(c->G_long, c->T_long, shift, px, c->sm_count, c->stream_excl, /*longdoc=*/true,
                            /*exclusive_blocks=*/(c->n_excl + 3) / 4);
@@ -653,7 +687,7 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         pl.order = c->d_order + c->n_excl;
         pl.D = c->n_long - c->n_excl;
         pl.ticket = c->d_ticket + 1;
-        cudaError_t e = (c->long_kernel && !shift)
+        cudaError_t e = use_long
             ? launch_estep_long(c->K, pl, c->sm_count, c->stream_long)
             : launch_estep(c->G_long, c->T_long, shift, pl, c->sm_count, c->stream_long, /*longdoc=*/true);
         if (e != cudaSuccess)
@@ -760,6 +794,7 @@ static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
     memcpy(&nan_flag, c->h_pinned + 5, sizeof nan_flag);
     const double lik = c->h_pinned[1];
     c->alpha = c->h_pinned[4];
+    c->model_min = c->model_min_rowmax = -100.0;  // the table is lda_mle's now (floor: lda-model.c:42)
     c->stats.word_visits = (int64_t)c->h_pinned[3];
     float ms = 0;
     if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) c->stats.ms_estep_kernel = ms;
@@ -817,6 +852,25 @@ extern "C" int oni_lda_get_logbeta(oni_lda_ctx *c, double *logbeta)
 {
     if (!c || !logbeta) return oni_set_error(ONI_ERR_ARG, "get_logbeta: null argument");
     ONI_CUDA(cudaSetDevice(c->device));
+    {
+        // exp(digamma(gamma) + log beta) must be a normal number for at least one topic of every
+        // word, or the unshifted E-step normalises garbage (the reference's log_sum chain,
+        // lda-inference.c:53-64, has no such limit): remember how low this model goes
+        const size_t V = (size_t)c->V;
+        std::vector<double> rowmax(V, -INFINITY);
+        double lo = INFINITY;
+        for (int k = 0; k < c->K; k++) {
+            const double *row = logbeta + (size_t)k * V;
+            for (size_t w = 0; w < V; w++) {
+                const double x = row[w];
+                if (x != x) return oni_set_error(ONI_ERR_ARG, "model: log beta[%d][%zu] is NaN", k, w);
+                rowmax[w] = x > rowmax[w] ? x : rowmax[w];
+                lo = x < lo ? x : lo;
+            }
+        }
+        c->model_min = lo;
+        c->model_min_rowmax = *std::min_element(rowmax.begin(), rowmax.end());
+    }
     double *stage = nullptr;
     ONI_TRY(dev_alloc(&stage, (size_t)c->K * c->V));
     const dim3 grid((c->V + 31) / 32, (c->K + 31) / 32), block(32, 8);

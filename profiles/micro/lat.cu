@@ -25,6 +25,12 @@ __global__ void chain(double a, double b, double *out, long long *cyc, int *idx)
         if (OP == 7) { j = ((volatile int *)sm)[j & 1023] ; }         // LDS.32 chain
         if (OP == 8) { x = fma(x, b, a); x = __shfl_xor_sync(0xffffffffu, x, 1); }  // DFMA + SHFL
         if (OP == 9) { x = (double)__double2hiint(x); }               // I2F.F64 chain (with the mov)
+        if (OP == 11) {
+            double d0, d1;
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%4,%5};"
+                         : "=d"(d0), "=d"(d1) : "d"(x), "d"(b), "d"(a), "d"(a));
+            x = d0;
+        }
         if (OP == 10) { float f = (float)x; asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f)); x = (double)f; }
     }
     long long t1 = clock64();
@@ -50,12 +56,12 @@ int main()
     double *out; long long *cyc; int *idx;
     cudaMalloc(&out, 8 * 4096); cudaMalloc(&cyc, 8 * 64); cudaMalloc(&idx, 4 * 1024);
     long long h[16];
-    const char *names[] = {"DFMA", "DADD", "DMUL", "MUFU.RCP64H", "LDS.64+F2I", "SHFL.64", "hi-word IADD", "LDS.32", "DFMA+SHFL.64", "I2F.F64(hi)", "F2F+EX2+F2F"};
+    const char *names[] = {"DFMA", "DADD", "DMUL", "MUFU.RCP64H", "LDS.64+F2I", "SHFL.64", "hi-word IADD", "LDS.32", "DFMA+SHFL.64", "I2F.F64(hi)", "F2F+EX2+F2F", "DMMA.884 (d->a)"};
 #define RUN(op) chain<op><<<1, 32>>>(1.0000001, 0.9999999, out, cyc, idx); chain<op><<<1, 32>>>(1.0000001, 0.9999999, out, cyc, idx);
-    RUN(0) RUN(1) RUN(2) RUN(3) RUN(4) RUN(5) RUN(6) RUN(7) RUN(8) RUN(9) RUN(10)
+    RUN(0) RUN(1) RUN(2) RUN(3) RUN(4) RUN(5) RUN(6) RUN(7) RUN(8) RUN(9) RUN(10) RUN(11)
     cudaDeviceSynchronize();
     cudaMemcpy(h, cyc, sizeof h, cudaMemcpyDeviceToHost);
-    for (int i = 0; i < 11; i++) printf("%-16s %6.1f cycles per dependent step\n", names[i], (double)h[i] / N);
+    for (int i = 0; i < 12; i++) printf("%-16s %6.1f cycles per dependent step\n", names[i], (double)h[i] / N);
     for (int w = 1; w <= 16; w *= 2) {
         tput<<<1, 32 * w>>>(1.0000001, 0.9999999, out, cyc); tput<<<1, 32 * w>>>(1.0000001, 0.9999999, out, cyc);
         cudaDeviceSynchronize();
