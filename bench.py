@@ -7,11 +7,16 @@
 A step is ONE EM iteration (E-step over every document of the shard, the
 deterministic sufficient-statistics reduction, one all-reduce when N > 1, the
 M-step and the alpha Newton) on BASELINE.json's configs[1] ("flow day": 1M
-documents, 50k-word vocabulary, K=20) per GPU; with N GPUs every rank holds its
-own flow-day-sized shard of documents over the shared vocabulary (weak scaling),
-one process per GPU, and the K x V statistics are summed by one ncclAllReduce
-per iteration.  `value` = tokens (sum of counts) of all ranks x K / time of the K
-timed steps (device time, max over ranks), with the corpus resident in HBM.
+documents, 50k-word vocabulary, K=20).  With N GPUs that ONE corpus is cut into
+N contiguous shards balanced by pairs (strong scaling, what the reference does
+with its ranks, lda-estimate.c:201), one process per GPU, and the K x V
+statistics are summed by one ncclAllReduce per iteration; the weak-scaling
+figure (every rank its own flow-day-sized shard) rides along under "weak".
+`value` = tokens (sum of counts) of the job x K / time of the K timed steps
+(device time, max over ranks), with the corpus resident in HBM.  At N = 1 the
+line also carries `e2e_cli` (the `lda est` executable, text in, text out) and
+`scoring` (BASELINE configs[4]); at N > 1 `multi_gpu_parity` (the reference
+binary's golden run through this job's ranks before anything is timed).
 `e2e` = the same metric through the public C-ABI path from HOST buffers: corpus
 upload + index build + K EM iterations + gamma/beta readback.
 
@@ -214,8 +219,10 @@ def reference_arm(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args.gpus, {"sample": sample}),
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.gpus, {"sample": sample, "note": "the reference arm times a SAMPLE of the flow-day "
+                                              "generator (2500 documents per host core), not the 1M-document corpus: "
+                                              "its per-document sweep counts differ from the full run's"}),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": nproc, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -274,36 +281,45 @@ def our_arm(args):
     return 0
 
 
-def _our_arm(args):
+def _em_corpus(args, shape, scaling, rank, world, dev):
+    """This rank's documents as device CSR tensors.  strong: ONE corpus of the named shape, the
+    same on every rank (same seed), cut into contiguous shards balanced by pair count
+    (oni_ml_b200.dist.shard_bounds = shard_docs of csrc/engine.cu) -- what the reference does with
+    its ranks, lda-estimate.c:201.  weak: every rank draws its own documents over shared topics."""
+    import torch
+    from oni_ml_b200 import dist as odist
+    from oni_ml_b200.corpus import synth_corpus
+    V = WORKLOAD["vocab"]
+    kw = dict(k_true=K_TOPICS, mu=WORKLOAD["mu"], geom_p=WORKLOAD["geom_p"], dup_frac=shape.get("dup_frac", 0.02),
+              device=dev, as_torch=True)
+    if scaling == "strong":
+        total = args.docs or shape.get("docs_total", WORKLOAD["docs_per_gpu"])
+        ptr, word, count = synth_corpus(total, V, seed=20160123, **kw)
+        cut = odist.shard_bounds(ptr.cpu().numpy(), world)
+        lo, hi = cut[rank], cut[rank + 1]
+        a, b = int(ptr[lo]), int(ptr[hi])
+        ptr, word, count = (ptr[lo:hi + 1] - a).contiguous(), word[a:b].contiguous(), count[a:b].contiguous()
+        torch.cuda.empty_cache()
+        return ptr, word, count, total
+    D = args.docs or WORKLOAD["docs_per_gpu"]
+    # ranks hold shards of ONE corpus: rank 0's single stream draws the topics first, the other
+    # ranks draw the same topics from a stream of their own
+    ptr, word, count = synth_corpus(D, V, seed=20160123 + rank, topic_seed=None if rank == 0 else 20160123, **kw)
+    return ptr, word, count, D * world
+
+
+def _em_measure(args, shape, scaling, rank, world, local, dev, with_e2e):
+    """Time args.steps EM iterations (device events on the engine's stream, max over ranks) and,
+    with_e2e, one whole job from pinned host CSR.  Returns a dict (the same on every rank for
+    the global figures)."""
     import torch
     import torch.distributed as dist
     from oni_ml_b200 import _lib, dist as odist, lda
-    from oni_ml_b200.corpus import Corpus, synth_corpus
+    from oni_ml_b200.corpus import Corpus
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU path")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    _lib.load()
-
-    shape = SHAPES[args.shape]
-    global K_TOPICS
-    K_TOPICS = shape["topics"]
-    WORKLOAD["vocab"], WORKLOAD["mu"] = shape["vocab"], shape["mu"]
-    if "docs_total" in shape:  # fixed total: month-scale is defined on 8 GPUs, DNS day on the GPUs given
-        WORKLOAD["docs_per_gpu"] = shape["docs_total"] // (8 if args.shape == "month" else world)
-    D, V = args.docs or WORKLOAD["docs_per_gpu"], WORKLOAD["vocab"]
-    ptr, word, count = synth_corpus(D, V, k_true=K_TOPICS, mu=WORKLOAD["mu"], geom_p=WORKLOAD["geom_p"],
-                                    dup_frac=shape.get("dup_frac", 0.02), seed=20160123 + rank, device=dev,
-                                    as_torch=True,
-                                    # ranks hold shards of ONE corpus: rank 0's single stream draws the topics
-                                    # first, the other ranks draw the same topics from a stream of their own
-                                    topic_seed=None if rank == 0 else 20160123)
+    V = WORKLOAD["vocab"]
+    ptr, word, count, docs_total = _em_corpus(args, shape, scaling, rank, world, dev)
+    D = int(ptr.numel()) - 1
     nnz = int(word.numel())
     tokens = int(count.sum(dtype=torch.int64))
     st = _lib.Settings(20, 1e-6, 10_000, 1e-6, 1)  # shipped thresholds; the loop count is ours
@@ -321,8 +337,10 @@ def _our_arm(args):
             dist.barrier()
             torch.cuda.synchronize(dev)
 
+    visits_log = []
     for _ in range(args.warmup):
         odist.em_iteration(eng)
+        visits_log.append(eng.stats()["word_visits"])
     sync_all()
     launches0 = eng.stats()["kernel_launches"]
     sampler = ClockSampler(local)
@@ -334,25 +352,52 @@ def _our_arm(args):
     for _ in range(args.steps):
         lik, conv = odist.em_iteration(eng)
         s = eng.stats()
-        per_step.append((s["ms_estep_kernel"], s["ms_suffstats"], s["ms_mstep"], s["word_visits"], lik))
+        per_step.append(dict(s, lik=lik))
     e1.record(stream)
     sync_all()
     clocks = sampler.stop() if rank == 0 else None
     ms_total = e0.elapsed_time(e1)
     launches = eng.stats()["kernel_launches"] - launches0
-    t = torch.tensor([ms_total, float(tokens), float(nnz)], dtype=torch.float64, device=dev)
-    my_estep = statistics.mean(p[0] for p in per_step)
-    per_rank = [my_estep]
+    if rank == 0:  # (profiles/summarize_ncu.py json wants the visits of the launch ncu captured)
+        print("[bench] %s: word visits per E-step launch set of rank 0, warm-up first: %s"
+              % (scaling, visits_log + [p["word_visits"] for p in per_step]), file=sys.stderr)
+
+    def mean(key):
+        return statistics.mean(p[key] for p in per_step)
+    mine = [ms_total, float(tokens), float(nnz), float(launches), mean("ms_estep_kernel"), mean("ms_end_exclusive"),
+            mean("ms_end_long"), mean("ms_end_main"), float(per_step[-1]["longest_doc_pairs"]),
+            float(per_step[-1]["docs_exclusive"]), float(per_step[-1]["docs_long"]), mean("word_visits"), float(D),
+            mean("ms_suffstats"), mean("ms_mstep")]
+    t = torch.tensor(mine, dtype=torch.float64, device=dev)
+    rows = [t]
     if world > 1:
-        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        ms_total, tokens_all, nnz_all = float(tmax[0]), float(tsum[1]), float(tsum[2])
-        allr = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
-        dist.all_gather(allr, torch.tensor([my_estep], dtype=torch.float64, device=dev))
-        per_rank = [float(x[0]) for x in allr]
-    else:
-        tokens_all, nnz_all = float(tokens), float(nnz)
-    value = tokens_all * args.steps / (ms_total * 1e-3)
+        rows = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(rows, t)
+    rows = [r.tolist() for r in rows]
+    ms_total = max(r[0] for r in rows)
+    tokens_all, nnz_all = sum(r[1] for r in rows), sum(r[2] for r in rows)
+    out = {
+        "scaling": scaling, "ms_total": ms_total, "ms_per_step": ms_total / args.steps,
+        "value": tokens_all * args.steps / (ms_total * 1e-3), "tokens_all": tokens_all, "nnz_all": nnz_all,
+        "docs_total": docs_total, "docs": D, "nnz": nnz, "tokens": tokens, "launches": int(sum(r[3] for r in rows)),
+        "clocks": clocks, "ms_estep": rows[0][4], "visits": sum(r[11] for r in rows), "visits_rank0": rows[0][11],
+        "ms_suffstats": rows[0][13], "ms_mstep": rows[0][14],
+        "per_rank": {
+            "estep_ms": [round(r[4], 2) for r in rows],
+            # ends of the E-step's three overlapping launches, ms after its start (-1: not launched)
+            "end_exclusive_ms": [round(r[5], 2) for r in rows], "end_long_ms": [round(r[6], 2) for r in rows],
+            "end_main_ms": [round(r[7], 2) for r in rows],
+            "longest_doc_pairs": [int(r[8]) for r in rows],
+            "docs_exclusive": [int(r[9]) for r in rows], "docs_long": [int(r[10]) for r in rows],
+            "docs": [int(r[12]) for r in rows], "pairs": [int(r[2]) for r in rows],
+            "word_visits": [int(r[11]) for r in rows],
+        },
+    }
+    if not with_e2e:
+        eng.close()
+        del ptr, word, count
+        torch.cuda.empty_cache()
+        return out
 
     # ---- e2e: host buffers -> engine -> host results, K EM iterations.
     # The engine handle (and with it the NCCL communicator of a multi-GPU job) is the long-lived
@@ -365,7 +410,7 @@ def _our_arm(args):
     # result buffers the caller owns and reuses from job to job: pinned, like the inputs
     gam_out = torch.empty((D, K_TOPICS), dtype=torch.float64).pin_memory().numpy()
     lb_out = torch.empty((K_TOPICS, V), dtype=torch.float64).pin_memory().numpy()
-    # one untimed job set-up first (re-allocating the 9 GB of engine buffers was seen to take 30 ms
+    # one untimed job set-up first (re-allocating the engine buffers was seen to take 30 ms
     # or 300 ms; the timed pass should not depend on which)
     eng.set_corpus(host)
     eng.init_random(SEED, ALPHA)
@@ -388,77 +433,222 @@ def _our_arm(args):
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = tokens_all * args.steps / float(te[0])
+    out["e2e_s"] = float(te[0])
+    out["e2e_value"] = tokens_all * args.steps / float(te[0])
     # bytes the engine uploads: word + count (4 + 4 per pair), doc_ptr (8 per document); the
     # chunk lists of the reduction are a few MB more
-    h2d = (8 * nnz + 8 * (D + 1)) / args.steps
-    d2h = (gam.nbytes + lb.nbytes) / args.steps + 48
+    out["h2d"] = (8 * nnz + 8 * (D + 1)) / args.steps
+    out["d2h"] = (gam.nbytes + lb.nbytes) / args.steps + 48
+    out["host_corpus"] = host
+    return out
+
+
+def multi_gpu_parity(rank, world, local, dev):
+    """Before anything is timed at N > 1: the committed golden run of the reference binary
+    (tests/golden/c0_k20: 403 documents, K=20, shipped settings, 21 EM iterations) through THIS
+    job's ranks and NCCL all-reduce -- likelihood trajectory and final gamma against the
+    reference's own files.  Returns the largest relative error over all ranks."""
+    import torch
+    import torch.distributed as dist
+    from oni_ml_b200 import _lib, dist as odist, files, lda
+    g = os.path.join(ROOT, "tests", "golden")
+    c = lda.read_corpus(os.path.join(g, "c0_model.dat"))
+    st = lda.read_settings(os.path.join(g, "c0_k20", "settings.txt"))
+    cut = odist.shard_bounds(c.doc_ptr, world)
+    mine = c.slice_docs(cut[rank], cut[rank + 1])
+    want_lik = files.read_likelihood(os.path.join(g, "c0_k20", "likelihood.dat"))[:, 0]
+    want_gam = files.read_matrix(os.path.join(g, "c0_k20", "final.gamma"))[cut[rank]:cut[rank + 1]]
+    with lda.LdaEngine(local, 20, c.num_terms, st) as eng:
+        eng.set_corpus(mine)
+        eng.init_random(4357, 2.5)
+        odist.bootstrap_nccl(eng, rank, world)
+        lik, _ = odist.run_em(eng)
+        gam = eng.gamma()
+    err = 1.0
+    if len(lik) == len(want_lik):
+        err = float(np.max(np.abs((np.asarray(lik) - want_lik) / want_lik)))
+        if gam.size:
+            err = max(err, float(np.max(np.abs(gam - want_gam) / (np.abs(want_gam) + 1e-4))))
+    t = torch.tensor([err], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return {"max_rel_err": float(t[0]), "against": "tests/golden/c0_k20 (the reference binary's likelihood.dat and final.gamma)",
+            "tolerance": 1e-6, "ranks": world, "em_iterations": len(lik)}
+
+
+def e2e_cli_leg(host_corpus):
+    """The drop-in boundary itself (ml_ops.sh:80): wall time of `lda est 2.5 20 settings.txt 1
+    model.dat random <outdir>` from the model.dat text to final.beta / final.gamma / final.other
+    / likelihood.dat on disk, shipped settings (EM to convergence, at most 21 iterations)."""
+    from oni_ml_b200 import LDA_BIN, lda
+    work = tempfile.mkdtemp(prefix="oni_cli_")
+    try:
+        model = os.path.join(work, "model.dat")
+        lda.write_corpus(model, host_corpus)  # untimed: the pre-LDA stage leaves this file behind
+        st = os.path.join(work, "settings.txt")
+        with open(st, "w") as f:
+            f.write(SETTINGS_TXT % 20)
+        out = os.path.join(work, "out")
+        t0 = time.perf_counter()
+        p = subprocess.run([LDA_BIN, "est", str(ALPHA), str(K_TOPICS), st, "1", model, "random", out],
+                           env=dict(os.environ, ONI_LDA_SEED=str(SEED)), stdout=subprocess.DEVNULL,
+                           stderr=subprocess.PIPE, text=True)
+        wall = time.perf_counter() - t0
+        if p.returncode != 0:
+            return {"error": "lda est exited %d: %s" % (p.returncode, p.stderr[-300:])}
+        iters = open(os.path.join(out, "likelihood.dat")).read().count("\n")
+        sizes = {n: os.path.getsize(os.path.join(out, n)) for n in ("final.gamma", "final.beta")}
+        return {"seconds": wall, "em_iterations": iters, "value": host_corpus.tokens * iters / wall, "unit": UNIT,
+                "model_dat_bytes": os.path.getsize(model), "final_gamma_bytes": sizes["final.gamma"],
+                "final_beta_bytes": sizes["final.beta"],
+                "what": "process wall time of the drop-in executable, model.dat text in, final.* text out"}
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
+def _our_arm(args):
+    import torch
+    import torch.distributed as dist
+    from oni_ml_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+
+    shape = SHAPES[args.shape]
+    global K_TOPICS
+    K_TOPICS = shape["topics"]
+    WORKLOAD["vocab"], WORKLOAD["mu"] = shape["vocab"], shape["mu"]
+    if "docs_total" in shape:  # month-scale is defined on 8 GPUs: this run holds 1/8 of it per GPU
+        WORKLOAD["docs_per_gpu"] = shape["docs_total"] // (8 if args.shape == "month" else world)
+    # ONE corpus cut over the ranks is what the reference does with its ranks and what the
+    # north star asks of 1 -> 8 GPUs; month-scale documents are drawn per rank (a 20M-document
+    # corpus does not fit one GPU to be cut there)
+    scaling = args.scaling or ("weak" if args.shape == "month" else "strong")
+    V = WORKLOAD["vocab"]
+
+    parity = multi_gpu_parity(rank, world, local, dev) if world > 1 else None
+    m = _em_measure(args, shape, scaling, rank, world, local, dev, with_e2e=True)
+    weak = None
+    if world > 1 and scaling == "strong" and not args.no_weak:
+        # the weak-scaling line of round 1 (every rank its own flow-day-sized shard), kept beside
+        w = _em_measure(args, shape, "weak", rank, world, local, dev, with_e2e=False)
+        weak = {"value": w["value"], "unit": UNIT, "ms_per_step": w["ms_per_step"], "docs_per_gpu": w["docs"],
+                "estep_ms_per_rank": w["per_rank"]["estep_ms"], "scaling": "weak"}
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return None
-    ms_estep = statistics.mean(p[0] for p in per_step)
-    visits = statistics.mean(p[3] for p in per_step)
+    D, nnz, tokens = m["docs"], m["nnz"], m["tokens"]
+    ms_estep, visits0 = m["ms_estep"], m["visits_rank0"]
     peak, peak_src = peaks()
-    # algorithmic bytes of the E-step kernel per launch: tokens 8/pair read, final phi
+    # algorithmic bytes of rank 0's E-step launch (DESIGN.md 4.1): tokens 8/pair read, final phi
     # 8K/pair written, gamma 8K/doc written, log-beta table 8KV read once
     alg_bytes = nnz * (8 + 8 * K_TOPICS) + 8 * K_TOPICS * D + 8 * K_TOPICS * V
     achieved = alg_bytes / (ms_estep * 1e-3) / 1e9
+    prof = ncu_profile_record()
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    roof = {"bound": "hbm", "kernel": "estep_kernel<G=4,T=5>" if K_TOPICS == 20 else "estep_kernel (K=%d)" % K_TOPICS,
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": int(alg_bytes), "ms_per_launch": ms_estep,
+            "traffic": None, "dram_frac": None}
+    if prof and K_TOPICS == 20:
+        # dram bytes and FP64 instructions per word visit, read from the ncu report of THIS build
+        # (profiles/summarize_ncu.py json; refused when the kernel sources have changed since)
+        roof["traffic"] = int(prof["dram_bytes_per_visit"] * visits0)
+        roof["dram_frac"] = prof["dram_bytes_per_visit"] * visits0 / (ms_estep * 1e-3) / 1e9 / peak
+        roof["traffic_source"] = "ncu dram__bytes per word visit (%s) x this launch's visits" % prof["file"]
+        roof["fp64_pipe_pct_under_ncu"] = prof.get("fp64_pipe_pct")
+        roof["fp64"] = fp64_roofline(visits0, ms_estep, m["clocks"], sms, prof["fp64_lane_ops_per_visit"])
+    elif K_TOPICS == 20:
+        roof["traffic_source"] = "no ncu record of the current kernel sources under profiles/ (stale ones are refused)"
+    roof["note"] = ("fp64-pipe bound, not HBM bound: %.3g (word,topic) visits per launch, each a digamma+exp in fp64"
+                    % (visits0 * K_TOPICS))
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(world, {"pairs_per_gpu": nnz, "tokens_per_gpu": tokens, "shape": args.shape,
-                                          "workload": (shape["name"] % D) + ", ~%.0fM (doc,word) pairs per GPU, %d-word "
-                                          "vocabulary, K=%d, alpha=%.1f, settings.txt as shipped; one step = one EM "
-                                          "iteration" % (nnz / 1e6, V, K_TOPICS, ALPHA)}),
-        "em_iters_per_sec": args.steps / (ms_total * 1e-3),
-        "pairs_per_sec": nnz_all * args.steps / (ms_total * 1e-3),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "seconds": float(te[0]),
+        "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": m["ms_per_step"], "higher_is_better": True,
+        "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(world, {
+            "docs_total": m["docs_total"], "docs_per_gpu": D, "pairs_per_gpu": nnz, "tokens_per_gpu": tokens,
+            "shape": args.shape,
+            "workload": (shape["name"] % D) + ", %d documents / %.1fM (doc,word) pairs / %.0fM tokens in the job, %d-word "
+            "vocabulary, K=%d, alpha=%.1f, settings.txt as shipped; one step = one EM iteration; %s" % (
+                m["docs_total"], m["nnz_all"] / 1e6, m["tokens_all"] / 1e6, V, K_TOPICS, ALPHA,
+                "ONE corpus cut into %d contiguous shards balanced by pairs (strong scaling)" % world
+                if scaling == "strong" else "every rank holds its own shard of this size (weak scaling)")}),
+        "em_iters_per_sec": args.steps / (m["ms_total"] * 1e-3),
+        "pairs_per_sec": m["nnz_all"] * args.steps / (m["ms_total"] * 1e-3),
+        "e2e": {"value": m["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": int(m["h2d"]),
+                "d2h_bytes_per_step": int(m["d2h"]), "seconds": m["e2e_s"],
                 "what": "one job on a live LdaEngine from pinned host CSR: upload + index build + model init + %d EM iterations + gamma/beta readback into pinned buffers" % args.steps},
-        "gpu_launches": int(launches),
-        "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "estep_kernel<G=4,T=5>" if K_TOPICS == 20 else "estep_kernel (K=%d)" % K_TOPICS, "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak,
-                     # ncu --set full, profiles/r1_estep_final.txt: dram read+write = 316 B per word visit
-                     # (the phi row of every sweep streams through HBM); scaled to this launch's visits
-                     "traffic": int(316.4 * visits / world), "traffic_source": "ncu dram__bytes per word visit x visits of this launch",
-                     # what the launch actually moves through HBM against the same peak (the phi rows of every sweep)
-                     "dram_frac": 316.4 * visits / world / (ms_estep * 1e-3) / 1e9 / peak,
-                     "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": int(alg_bytes), "ms_per_launch": ms_estep,
-                     "fp64_pipe": "56 % busy (ncu sm__pipe_fp64_cycles_active), 240 FP64 of 474 instructions per warp word-visit",
-                     # the limiter, measured live: FP64 lane-operations of the visit body (SASS count:
-                     # 141 DFMA + 51 DMUL + 48 DADD per warp visit of 8 documents = 960 per word visit)
-                     # x this launch's visits / launch time, against SMs x 64 FP64 lanes x the SM clock
-                     # sampled during the timed region
-                     "fp64": fp64_roofline(visits / world, ms_estep, clocks, torch.cuda.get_device_properties(dev).multi_processor_count) if K_TOPICS == 20 else None,
-                     "note": "fp64-pipe bound, not HBM bound: %.3g (word,topic) visits per launch, each a "
-                             "digamma+exp in fp64" % (visits * K_TOPICS)},
-        "breakdown_ms": {"estep_kernel": ms_estep, "suffstats": statistics.mean(p[1] for p in per_step),
-                         "mstep": statistics.mean(p[2] for p in per_step)},
-        "word_visits_per_step": visits,
-        "estep_ms_per_rank": [round(x, 2) for x in per_rank],
+        "gpu_launches": m["launches"],
+        "clocks": m["clocks"],
+        "roofline": roof,
+        "breakdown_ms": {"estep_kernel": ms_estep, "suffstats": m["ms_suffstats"], "mstep": m["ms_mstep"]},
+        "word_visits_per_step": m["visits"],
+        "estep_ms_per_rank": m["per_rank"]["estep_ms"],
+        "per_rank": m["per_rank"],
     }
+    if parity:
+        line["multi_gpu_parity"] = parity
+    if weak:
+        line["weak"] = weak
     if world == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_baseline_leg()
         except Exception as e:  # the GPU numbers stand on their own
             line["cpu_baseline"] = {"error": str(e)}
+    if world == 1 and args.shape == "flow_day" and not args.no_cli:
+        try:
+            line["e2e_cli"] = e2e_cli_leg(m["host_corpus"])
+        except Exception as e:
+            line["e2e_cli"] = {"error": str(e)}
     if world > 1:
         dist.destroy_process_group()
     return line
 
 
-def fp64_roofline(visits_per_gpu, ms, clocks, sms):
-    lane_ops = 960.0 * visits_per_gpu
+def kernel_source_hash():
+    """sha256 over the E-step kernel sources: an ncu record only describes the build it was taken from."""
+    import hashlib
+    h = hashlib.sha256()
+    src = os.path.join(ROOT, "oni_ml_b200", "csrc")
+    for name in ("estep.cuh", "devmath.cuh", "math_tables.h", "estep_inst.inc"):
+        with open(os.path.join(src, name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_profile_record():
+    """profiles/estep_ncu.json (written by `profiles/summarize_ncu.py json <report>` from an
+    `ncu --set full` capture of bench.py): per-word-visit DRAM bytes and FP64 instruction count
+    of the main E-step launch.  None when absent or taken from other kernel sources."""
+    path = os.path.join(ROOT, "profiles", "estep_ncu.json")
+    try:
+        with open(path) as f:
+            rec = json.load(f)
+    except Exception:
+        return None
+    if rec.get("source_hash") != kernel_source_hash():
+        return None
+    rec["file"] = "profiles/estep_ncu.json"
+    return rec
+
+
+def fp64_roofline(visits_per_gpu, ms, clocks, sms, lane_ops_per_visit):
+    lane_ops = lane_ops_per_visit * visits_per_gpu
     achieved = lane_ops / (ms * 1e-3) / 1e9
     mhz = (clocks or {}).get("sm_mhz") or 0
     peak = sms * 64 * mhz * 1e6 / 1e9 if mhz else None
     return {"achieved": achieved, "peak": peak, "unit": "G fp64 lane-ops/s (an FMA counts once)",
-            "frac": (achieved / peak) if peak else None, "lane_ops_per_word_visit": 960,
+            "frac": (achieved / peak) if peak else None, "lane_ops_per_word_visit": lane_ops_per_visit,
             "peak_source": "%d SMs x 64 FP64 lanes x %.0f MHz (median SM clock under load)" % (sms, mhz)}
 
 
@@ -636,6 +826,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--docs", type=int, default=0, help="documents per GPU (default: the flow-day 1M)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cli", action="store_true", help="skip the e2e_cli leg (the `lda est` executable on a flow-day model.dat)")
+    ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the extra weak-scaling measurement")
+    ap.add_argument("--no-scoring", action="store_true", help="N = 1: skip the attached scoring record (BASELINE configs[4])")
+    ap.add_argument("--scaling", default=None, choices=["strong", "weak"],
+                    help="strong (default): ONE corpus cut over the ranks; weak: every rank its own shard")
     ap.add_argument("--workload", default="em", choices=["em", "score"],
                     help="em (default, the headline metric) or score (BASELINE configs[4])")
     ap.add_argument("--events", type=int, default=250_000_000, help="events for --workload score")

@@ -82,6 +82,9 @@ typedef struct {
  * library; release them with oni_lda_free_corpus. */
 int oni_lda_read_corpus(const char *model_dat_path, oni_lda_corpus *out);
 void oni_lda_free_corpus(oni_lda_corpus *c);
+/* The same text written from CSR arrays: one line per document, "N w:c w:c ...", as
+ * lda_pre.py:94 writes it and read_data (lda-data.c:35-51) parses it. */
+int oni_lda_write_corpus(const char *model_dat_path, const oni_lda_corpus *c);
 
 /* The corpus indexing stage, lda_pre.py (ml_ops.sh:67): reads <dir>doc_wc.dat
  * ("ip,word,count" rows) and writes <dir>words.dat, <dir>doc.dat and <dir>model.dat
@@ -206,6 +209,15 @@ typedef struct {
     double ms_mstep;         /* M-step + alpha kernels                        */
     int64_t word_visits;     /* sum over docs of pairs x passes               */
     int64_t kernel_launches; /* kernels launched by the library so far        */
+    /* where the E-step's time goes: its three launches overlap on three streams; each   */
+    /* figure is the time from the start of the E-step to the END of that launch (ms;   */
+    /* -1 = not launched).  A shard's longest documents are serial chains of word visits */
+    /* (lda-inference.c:50-75) and pace a small shard.                                   */
+    double ms_end_exclusive; /* the longest documents, alone on their SMs     */
+    double ms_end_long;      /* the other long documents, one per warp        */
+    double ms_end_main;      /* everything else                               */
+    int32_t docs_exclusive, docs_long; /* how many documents each of the two took */
+    int64_t longest_doc_pairs;         /* pairs of the shard's longest document   */
 } oni_lda_stats;
 int oni_lda_get_stats(oni_lda_ctx *ctx, oni_lda_stats *out);
 /* The CUDA stream (cudaStream_t) every kernel of this context is launched on,

@@ -56,7 +56,9 @@ class ResultC(C.Structure):
 class StatsC(C.Structure):
     _fields_ = [("ms_estep_kernel", C.c_double), ("ms_suffstats", C.c_double),
                 ("ms_mstep", C.c_double), ("word_visits", C.c_int64),
-                ("kernel_launches", C.c_int64)]
+                ("kernel_launches", C.c_int64),
+                ("ms_end_exclusive", C.c_double), ("ms_end_long", C.c_double), ("ms_end_main", C.c_double),
+                ("docs_exclusive", C.c_int32), ("docs_long", C.c_int32), ("longest_doc_pairs", C.c_int64)]
 
 
 _vp = C.c_void_p
@@ -69,6 +71,7 @@ SIGNATURES = {
     "oni_lda_read_settings": (C.c_int, [C.c_char_p, C.POINTER(Settings)]),
     "oni_lda_read_corpus": (C.c_int, [C.c_char_p, C.POINTER(CorpusC)]),
     "oni_lda_free_corpus": (None, [C.POINTER(CorpusC)]),
+    "oni_lda_write_corpus": (C.c_int, [C.c_char_p, C.POINTER(CorpusC)]),
     "oni_lda_pre": (C.c_int, [C.c_char_p]),
     "oni_lda_main": (C.c_int, [C.c_int, C.POINTER(C.c_char_p)]),
     "oni_lda_estimate": (C.c_int, [C.POINTER(CorpusC), _i32, _f64, C.POINTER(Settings), C.c_uint32,

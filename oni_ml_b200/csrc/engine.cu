@@ -100,6 +100,7 @@ struct oni_lda_ctx {
     int G_long = 32;       // long documents get wider groups: G_long lanes, T_long topics per lane
     int T_long = 0;
     int long_min = 0;      // documents with at least this many pairs are "long" (0 = none)
+    bool long_min_auto = false;  // ... chosen per corpus from its size (no ONI_LDA_LONG_DOC)
     int32_t n_long = 0;    // they are the first n_long entries of `order`
     int32_t n_excl = 0;    // the first n_excl of those get an SM to themselves (4 documents per SM)
     oni_lda_settings st{};
@@ -218,23 +219,37 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     for (int32_t d = 0; d < D; d++)
         if (h_ptr[d + 1] < h_ptr[d]) return oni_set_error(ONI_ERR_ARG, "doc_ptr not monotone at %d", d);
     if (h_ptr[0] != 0 || h_ptr[D] != nnz) return oni_set_error(ONI_ERR_ARG, "doc_ptr does not span the pairs");
+    // Three tiers, by the length of a document's serial chain of word visits against the time
+    // the shard's bulk takes (~1.6 ns per pair on one B200 at K = 20):
+    //   main      12 warps per SM, 8 documents per warp: ~1.3 us per visit of one document
+    //   long      estep_long_kernel, one document per warp, its blocks of four warps sharing SMs
+    //             with the main launch's: ~0.35 us per visit
+    //   longest   the same kernel alone on its SMs (one warp per scheduler): 0.2 us per visit
+    // A document moves up a tier when its chain at the lower tier's pace would last ~0.8 of the
+    // bulk time: from nnz/19000 pairs to the long tier (flow day on one GPU: capped at 1024; an
+    // eighth of it: 360), from nnz/6000 to the top one.  (Measured and dropped for the middle
+    // tier: the main build with one block per SM -- a lone warp of it runs at 1.7 us per visit,
+    // slower than at full occupancy -- and twelve long-kernel warps per SM, see estep_long.cuh.)
+    // ONI_LDA_LONG_DOC / ONI_LDA_EXCL_DOC override the two thresholds (0 = tier off).
+    int long_min = c->long_min;
+    if (c->long_min_auto && c->long_kernel) long_min = (int)std::min<int64_t>(1024, std::max<int64_t>(128, nnz / 19000));
     int32_t n_long = 0;
-    if (c->long_min > 0)
-        for (int32_t d = 0; d < D; d++) n_long += (h_ptr[d + 1] - h_ptr[d]) >= c->long_min;
-    int64_t max_pairs = 0;
-    for (int32_t d = 0; d < D; d++) max_pairs = std::max<int64_t>(max_pairs, h_ptr[d + 1] - h_ptr[d]);
-    // A document long enough for its serial chain of word visits to outlast the rest of the
-    // E-step sets the pace of the whole launch, and twice over when its warp shares a scheduler
-    // with busy warps.  The few longest documents therefore get SMs to themselves.  Default
-    // threshold: 1/20000 of the shard's pairs (what a chain can cover while the rest runs);
-    // at most 1/8 of the SMs are given away.  ONI_LDA_EXCL_DOC overrides (0 = off).
+    int64_t pairs_long = 0, max_pairs = 0;
+    for (int32_t d = 0; d < D; d++) {
+        const int64_t n = h_ptr[d + 1] - h_ptr[d];
+        max_pairs = std::max(max_pairs, n);
+        if (long_min > 0 && n >= long_min) { n_long++; pairs_long += n; }
+    }
     int32_t n_excl = 0;
+    int64_t pairs_excl = 0;
     if (n_long > 0 && c->G_long == 32 && c->T_long <= 4) {
         const char *env = getenv("ONI_LDA_EXCL_DOC");
-        const int64_t excl_min = env ? atoll(env) : std::max<int64_t>(c->long_min, nnz / 20000);
+        const int64_t excl_min = env ? atoll(env) : std::max<int64_t>(long_min, nnz / (c->long_kernel ? 6000 : 20000));
         if (excl_min > 0)
-            for (int32_t d = 0; d < D; d++) n_excl += (h_ptr[d + 1] - h_ptr[d]) >= excl_min;
-        n_excl = std::min<int32_t>({n_excl, n_long, 4 * std::max(1, c->sm_count / 8)});
+            for (int32_t d = 0; d < D; d++)
+                if (h_ptr[d + 1] - h_ptr[d] >= excl_min) { n_excl++; pairs_excl += h_ptr[d + 1] - h_ptr[d]; }
+        const int32_t cap = std::min<int32_t>(n_long, 4 * std::max(1, c->sm_count / 8));  // at most 1/8 of the SMs
+        if (n_excl > cap) { n_excl = cap; pairs_excl = 0; /* (only used for the middle tier's share below) */ }
     }
     tm.lap("validate doc_ptr");
 
@@ -445,8 +460,8 @@ static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_setti
     if (G < 32) {
         const char *env = getenv("ONI_LDA_LONG_DOC");
         c->long_min = env ? atoi(env) : 1024;
+        c->long_min_auto = !env;
         if (c->long_min > 0 && c->long_min < 64) c->long_min = 64;  // the long-document build requests rows 16 visits ahead
-        if (c->long_min > 0 && c->long_min < 16) c->long_min = 16;  // the long-document build queues rows several visits ahead
         const char *g = getenv("ONI_LDA_LONG_G");  // tuning knob: 8, 16 or 32
         c->G_long = (g && (atoi(g) == 8 || atoi(g) == 16) && atoi(g) > G) ? atoi(g) : 32;
         c->T_long = (K + c->G_long - 1) / c->G_long;
@@ -680,8 +695,8 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         ONI_CUDA(cudaEventRecord(c->ev_t_excl, c->stream_excl));
     }
     if (c->n_long > c->n_excl) {
-        // long documents next, one per warp, on a second stream so that the rest of
-        // the corpus fills the SMs as these drain
+        // the other long documents next, one per warp, on a second stream; their blocks (four
+        // warps) share SMs with the main launch's, so the rest of the corpus fills in around them
         ONI_CUDA(cudaStreamWaitEvent(c->stream_long, c->ev_fork, 0));
         EstepParams pl = p;
         pl.order = c->d_order + c->n_excl;
@@ -798,12 +813,15 @@ static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
     c->stats.word_visits = (int64_t)c->h_pinned[3];
     float ms = 0;
     if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) c->stats.ms_estep_kernel = ms;
-    if (getenv("ONI_LDA_TIMING")) {
+    {
         float a = -1, b = -1, m = -1;
         if (c->n_excl > 0) cudaEventElapsedTime(&a, c->ev[0], c->ev_t_excl);
         if (c->n_long > c->n_excl) cudaEventElapsedTime(&b, c->ev[0], c->ev_t_long);
-        cudaEventElapsedTime(&m, c->ev[0], c->ev_t_main);
-        fprintf(stderr, "[oni lda] E-step %.2f ms: exclusive (%d docs) done at %.2f, long (%d docs) at %.2f, rest at %.2f\n",
+        if (c->D > c->n_long) cudaEventElapsedTime(&m, c->ev[0], c->ev_t_main);
+        c->stats.ms_end_exclusive = a; c->stats.ms_end_long = b; c->stats.ms_end_main = m;
+        c->stats.docs_exclusive = c->n_excl; c->stats.docs_long = c->n_long - c->n_excl;
+        c->stats.longest_doc_pairs = c->max_doc_pairs;
+        if (getenv("ONI_LDA_TIMING")) fprintf(stderr, "[oni lda] E-step %.2f ms: exclusive (%d docs) done at %.2f, long (%d docs) at %.2f, rest at %.2f\n",
                 c->stats.ms_estep_kernel, c->n_excl, a, c->n_long - c->n_excl, b, m);
     }
     if (cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]) == cudaSuccess) c->stats.ms_suffstats = ms;

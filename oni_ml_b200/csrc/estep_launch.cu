@@ -7,14 +7,13 @@ cudaError_t launch_estep(int G, int T, bool shift, const EstepParams &p, int sm_
                          cudaStream_t stream, bool longdoc, int exclusive_blocks)
 {
     if (longdoc && G == 32 && T <= 4) return launch_estep_g32_long(T, shift, p, sm_count, stream, exclusive_blocks);
-    if (exclusive_blocks > 0) return cudaErrorInvalidValue;
     switch (G) {
-        case 1: return launch_estep_g1(T, shift, p, sm_count, stream);
-        case 2: return launch_estep_g2(T, shift, p, sm_count, stream);
-        case 4: return launch_estep_g4(T, shift, p, sm_count, stream);
-        case 8: return launch_estep_g8(T, shift, p, sm_count, stream);
-        case 16: return launch_estep_g16(T, shift, p, sm_count, stream);
-        case 32: return launch_estep_g32(T, shift, p, sm_count, stream);
+        case 1: return launch_estep_g1(T, shift, p, sm_count, stream, exclusive_blocks);
+        case 2: return launch_estep_g2(T, shift, p, sm_count, stream, exclusive_blocks);
+        case 4: return launch_estep_g4(T, shift, p, sm_count, stream, exclusive_blocks);
+        case 8: return launch_estep_g8(T, shift, p, sm_count, stream, exclusive_blocks);
+        case 16: return launch_estep_g16(T, shift, p, sm_count, stream, exclusive_blocks);
+        case 32: return launch_estep_g32(T, shift, p, sm_count, stream, exclusive_blocks);
         default: return cudaErrorInvalidValue;
     }
 }

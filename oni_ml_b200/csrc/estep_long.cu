@@ -7,23 +7,29 @@
 namespace oni {
 namespace {
 
-template <int T, int NSUM>
-cudaError_t launch_long(const EstepParams &p, int sm_count, cudaStream_t s, int exclusive_blocks)
+template <int T, int NSUM, int NW>
+cudaError_t launch_nw(const EstepParams &p, int sm_count, cudaStream_t s, int exclusive_blocks)
 {
-    auto kernel = estep_long_kernel<T, NSUM>;
+    auto kernel = estep_long_kernel<T, NSUM, NW>;
     int dev = 0, optin = 0;
     cudaError_t e;
     if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev)) != cudaSuccess) return e;
-    const int need = (int)LongLayout<T>::bytes;
+    const int need = (int)LongLayout<T, NW>::bytes;
     if (need > optin) return cudaErrorInvalidValue;
     // exclusive: ask for all the shared memory a block may have, so nothing shares the SM
     const int dyn = exclusive_blocks > 0 ? optin : need;
     if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn)) != cudaSuccess) return e;
-    const int want = (p.D + LONG_NW - 1) / LONG_NW;
+    const int want = (p.D + NW - 1) / NW;
     const int grid = exclusive_blocks > 0 ? exclusive_blocks : std::max(1, std::min(want, sm_count));
-    kernel<<<grid, LONG_NW * 32, dyn, s>>>(p);
+    kernel<<<grid, NW * 32, dyn, s>>>(p);
     return cudaGetLastError();
+}
+
+template <int T, int NSUM>
+cudaError_t launch_long(const EstepParams &p, int sm_count, cudaStream_t s, int exclusive_blocks)
+{
+    return launch_nw<T, NSUM, LONG_NW>(p, sm_count, s, exclusive_blocks);
 }
 
 }  // namespace

@@ -62,9 +62,12 @@ __device__ __forceinline__ void cp_async8_zfill(void *smem_dst, const void *gsrc
                  "l"(gsrc), "r"(bytes) : "memory");
 }
 
-constexpr int LONG_NW = 4;  // warps (documents) per block
-
-template <int T>
+// Warps (= documents) per block: one per scheduler.  More chains per scheduler were measured and
+// dropped: twelve warps per SM run at ~1360 cycles per visit each (the table reads, the sum's
+// broadcast loads and the ring take ~50 shared-memory wavefronts per visit, so twelve chains
+// saturate the SM's load/store pipe), a worse throughput than four warps at 383.
+constexpr int LONG_NW = 4;
+template <int T, int NW>
 struct LongLayout {
     static constexpr int QD = (T == 1) ? 8 : (T == 2) ? 4 : 2;  // visits ahead for the rows
     static constexpr int QT = 2 * QD;                           // ... and for the pairs
@@ -72,11 +75,11 @@ struct LongLayout {
     static constexpr size_t exk = psi + sizeof(double) * PSI_N * PSI_COEF;
     static constexpr size_t lg = exk + sizeof(double) * EXK_N;
     static constexpr size_t red = lg + sizeof(LogEntry) * ONI_MT_N;
-    static constexpr size_t keep = red + sizeof(double) * LONG_NW * 2 * 32;   // (S, c) of 32 visits
-    static constexpr size_t lb = keep + sizeof(double) * LONG_NW * 2 * 32;
-    static constexpr size_t old = lb + sizeof(double) * LONG_NW * QD * T * 32;
-    static constexpr size_t tk = old + sizeof(double) * LONG_NW * QD * T * 32;
-    static constexpr size_t bytes = tk + sizeof(int2) * LONG_NW * QT * 32;
+    static constexpr size_t keep = red + sizeof(double) * NW * 2 * 32;   // (S, c) of 32 visits
+    static constexpr size_t lb = keep + sizeof(double) * NW * 2 * 32;
+    static constexpr size_t old = lb + sizeof(double) * NW * QD * T * 32;
+    static constexpr size_t tk = old + sizeof(double) * NW * QD * T * 32;
+    static constexpr size_t bytes = tk + sizeof(int2) * NW * QT * 32;
 };
 
 struct LongShared {
@@ -95,7 +98,7 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
                                               const bool (&ok)[T], const int (&kk)[T], double alpha,
                                               double inv_k, double lik_const)
 {
-    constexpr int QD = LongLayout<T>::QD, QT = LongLayout<T>::QT;
+    constexpr int QD = LongLayout<T, 4>::QD, QT = LongLayout<T, 4>::QT;
     constexpr bool MASK = !(T == 1 && NSUM < 32);  // dead slots could reach the sum
     const unsigned full = 0xffffffffu;
     const int K = p.K, KP = p.KP;
@@ -343,10 +346,10 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
 
 // NSUM: how many per-lane partial sums the visit adds (32, or K when T == 1 and the host
 // promises K == NSUM: lanes >= K hold nothing).
-template <int T, int NSUM>
-__global__ void __launch_bounds__(LONG_NW * 32, 1) estep_long_kernel(const EstepParams p)
+template <int T, int NSUM, int NW>
+__global__ void __launch_bounds__(NW * 32, 1) estep_long_kernel(const EstepParams p)
 {
-    using L = LongLayout<T>;
+    using L = LongLayout<T, NW>;
     constexpr int QD = L::QD, QT = L::QT;
     extern __shared__ __align__(16) unsigned char smem[];
     {

@@ -455,6 +455,80 @@ int oni_lda_save_gamma(const char *path, int32_t d, int32_t k, const double *gam
     return write_matrix(path, gamma, d, k, 0);
 }
 
+/* ----------------------------------------------------------- model.dat writer */
+/* The inverse of oni_lda_read_corpus: "N w:c w:c ...\n" per document, the text lda_pre.py:94
+ * writes and read_data (lda-data.c:35-51) parses.  Documents are cut into a few ranges, each
+ * formatted by its own thread into its own buffer; the buffers are written in order. */
+typedef struct { const oni_lda_corpus *c; int32_t d0, d1; char *buf; size_t len; int failed; } wc_job;
+
+static char *put_u32(char *p, uint32_t v)
+{
+    char tmp[10];
+    int n = 0;
+    do { tmp[n++] = (char)('0' + v % 10); v /= 10; } while (v);
+    while (n) *p++ = tmp[--n];
+    return p;
+}
+
+static void *write_corpus_range(void *arg)
+{
+    wc_job *j = (wc_job *)arg;
+    const oni_lda_corpus *c = j->c;
+    const int64_t a = c->doc_ptr[j->d0], b = c->doc_ptr[j->d1];
+    /* per pair: blank + <=10 digits + ':' + <=10 digits; per document: <=10 digits + newline */
+    const size_t cap = (size_t)(b - a) * 22 + (size_t)(j->d1 - j->d0) * 11 + 16;
+    j->buf = (char *)malloc(cap);
+    if (!j->buf) { j->failed = 1; return NULL; }
+    char *p = j->buf;
+    for (int32_t d = j->d0; d < j->d1; d++) {
+        const int64_t lo = c->doc_ptr[d], hi = c->doc_ptr[d + 1];
+        p = put_u32(p, (uint32_t)(hi - lo));
+        for (int64_t i = lo; i < hi; i++) {
+            *p++ = ' ';
+            p = put_u32(p, (uint32_t)c->word[i]);
+            *p++ = ':';
+            p = put_u32(p, (uint32_t)c->count[i]);
+        }
+        *p++ = '\n';
+    }
+    j->len = (size_t)(p - j->buf);
+    return NULL;
+}
+
+int oni_lda_write_corpus(const char *path, const oni_lda_corpus *c)
+{
+    if (!path || !c || !c->doc_ptr || c->num_docs < 0) return oni_set_error(ONI_ERR_ARG, "write_corpus: bad argument");
+    for (int64_t i = 0; i < c->nnz; i++)
+        if (c->word[i] < 0 || c->count[i] < 0) return oni_set_error(ONI_ERR_ARG, "write_corpus: negative word id or count");
+    FILE *f = fopen(path, "w");
+    if (!f) return oni_set_error(ONI_ERR_IO, "cannot write %s: %s", path, strerror(errno));
+    enum { MAXT = 16 };
+    long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+    int nt = (int)(ncpu < 1 ? 1 : (ncpu > MAXT ? MAXT : ncpu));
+    if (c->nnz < (1 << 16)) nt = 1;
+    wc_job job[MAXT];
+    pthread_t th[MAXT];
+    int rc = ONI_OK;
+    for (int t = 0; t < nt; t++) {
+        /* ranges balanced by pairs */
+        const int64_t target0 = c->nnz * t / nt, target1 = c->nnz * (t + 1) / nt;
+        int32_t d0 = 0, d1 = c->num_docs;
+        if (t > 0) { int32_t lo = 0, hi = c->num_docs; while (lo < hi) { int32_t m = lo + (hi - lo) / 2; if (c->doc_ptr[m] < target0) lo = m + 1; else hi = m; } d0 = lo; }
+        if (t < nt - 1) { int32_t lo = 0, hi = c->num_docs; while (lo < hi) { int32_t m = lo + (hi - lo) / 2; if (c->doc_ptr[m] < target1) lo = m + 1; else hi = m; } d1 = lo; }
+        job[t].c = c; job[t].d0 = d0; job[t].d1 = d1 < d0 ? d0 : d1; job[t].buf = NULL; job[t].len = 0; job[t].failed = 0;
+        if (nt == 1 || pthread_create(&th[t], NULL, write_corpus_range, &job[t]) != 0) { write_corpus_range(&job[t]); th[t] = 0; }
+    }
+    for (int t = 0; t < nt; t++) {
+        if (nt > 1 && th[t]) pthread_join(th[t], NULL);
+        if (job[t].failed) rc = oni_set_error(ONI_ERR_NOMEM, "write_corpus: out of memory");
+        else if (rc == ONI_OK && fwrite(job[t].buf, 1, job[t].len, f) != job[t].len)
+            rc = oni_set_error(ONI_ERR_IO, "write failed on %s", path);
+        free(job[t].buf);
+    }
+    if (fclose(f) != 0 && rc == ONI_OK) rc = oni_set_error(ONI_ERR_IO, "write failed on %s", path);
+    return rc;
+}
+
 /* Test hook: the fast formatter against the C library on one value. */
 int oni_internal_format_fixed10(double v, char *out64)
 {

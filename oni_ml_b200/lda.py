@@ -57,6 +57,11 @@ def _corpus_c(corpus: Corpus) -> _lib.CorpusC:
     return c
 
 
+def write_corpus(path: str, corpus: Corpus) -> None:
+    """model.dat text of a corpus (lda_pre.py:94) through the library's threaded writer."""
+    check(_lib.load().oni_lda_write_corpus(path.encode(), C.byref(_corpus_c(corpus))))
+
+
 def estimate(corpus: Corpus, num_topics: int, alpha: float, settings: Settings, seed: int,
              ngpus: int = 1) -> dict:
     """oni_lda_estimate: run_em with ``random`` start over host buffers."""

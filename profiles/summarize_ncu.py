@@ -3,7 +3,14 @@
 
   python profiles/summarize_ncu.py launches <launches.csv>
   python profiles/summarize_ncu.py raw <report.ncu-rep>      (needs ncu on PATH)
+  python profiles/summarize_ncu.py json <report.ncu-rep> <word visits of the profiled launch> [kernel substring]
+      -> profiles/estep_ncu.json: what bench.py's roofline record reads (DRAM bytes and FP64
+         lane-operations per word visit of the main E-step launch), stamped with a hash of the
+         kernel sources so that bench.py refuses it once those change
 """
+import hashlib
+import json
+import os
 import csv
 import subprocess
 import sys
@@ -60,5 +67,65 @@ def raw(path):
         print("   stalls per issue: " + ", ".join("%s %.2f" % (n, x) for x, n in sorted(stalls, reverse=True)[:6]))
 
 
+def source_hash():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    h = hashlib.sha256()
+    for name in ("estep.cuh", "devmath.cuh", "math_tables.h", "estep_inst.inc"):  # = bench.py kernel_source_hash()
+        with open(os.path.join(root, "oni_ml_b200", "csrc", name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def to_json(path, visits, kernel="estep_kernel<4, 5"):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr = rows[0]
+    pick = [dict(zip(hdr, r)) for r in rows[2:] if kernel in dict(zip(hdr, r)).get("Kernel Name", "")]
+    if len(pick) != 1:
+        raise SystemExit("%d launches match %r in %s; capture exactly one (-k ... -c 1)" % (len(pick), kernel, path))
+    d = pick[0]
+    units = dict(zip(hdr, rows[1]))
+
+    def val(name):
+        v = float(d[name].replace(",", ""))
+        return v * {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "byte": 1.0,
+                    "ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(units[name], 1.0)
+    dram = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
+    # FP64 lane-operations: thread-level executions of every D* arithmetic instruction (source page)
+    src = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    srows = list(csv.reader(src.splitlines()))
+    h2 = next(r for r in srows if "Source" in r and "Thread Instructions Executed" in r)
+    i_src, i_thr, i_ins = h2.index("Source"), h2.index("Thread Instructions Executed"), h2.index("Instructions Executed")
+    lane_ops = warp_inst = fp64_inst = 0
+    for r in srows[srows.index(h2) + 1:]:
+        if len(r) <= i_thr or not r[i_thr].isdigit():
+            continue
+        op = r[i_src].split()
+        op = op[1] if op and op[0].startswith("@") else (op[0] if op else "")
+        warp_inst += int(r[i_ins])
+        if op.split(".")[0] in ("DFMA", "DMUL", "DADD"):
+            lane_ops += int(r[i_thr])
+            fp64_inst += int(r[i_ins])
+    rec = {
+        "kernel": d["Kernel Name"], "report": os.path.basename(path), "source_hash": source_hash(),
+        "launch_word_visits": visits, "duration_ms": val("gpu__time_duration.sum"),
+        "dram_bytes": dram, "dram_bytes_per_visit": dram / visits,
+        "fp64_lane_ops": lane_ops, "fp64_lane_ops_per_visit": lane_ops / visits,
+        "fp64_warp_instructions": fp64_inst, "warp_instructions": warp_inst,
+        "fp64_pipe_pct": float(d["sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"]),
+        "issue_active_pct": float(d["smsp__issue_active.avg.pct_of_peak_sustained_active"]),
+        "l2_hit_pct": float(d["lts__t_sector_hit_rate.pct"]),
+        "registers": int(d["launch__registers_per_thread"]),
+    }
+    dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "estep_ncu.json")
+    with open(dst, "w") as f:
+        json.dump(rec, f, indent=1)
+        f.write("\n")
+    print(json.dumps(rec, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2])
+    if sys.argv[1] == "json":
+        to_json(sys.argv[2], float(sys.argv[3]), *sys.argv[4:5])
+    else:
+        {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2])
