@@ -610,35 +610,46 @@ def _our_arm(args):
             line["e2e_cli"] = e2e_cli_leg(m["host_corpus"])
         except Exception as e:
             line["e2e_cli"] = {"error": str(e)}
+    if world == 1 and args.shape == "flow_day" and not args.no_scoring:
+        # BASELINE configs[4] under the same roof: the scoring record of `--workload score`
+        m.pop("host_corpus", None)
+        torch.cuda.empty_cache()
+        try:
+            line["scoring"] = _score_arm(args, attached=True)
+        except Exception as e:
+            line["scoring"] = {"error": str(e)}
     if world > 1:
         dist.destroy_process_group()
     return line
 
 
-def kernel_source_hash():
-    """sha256 over the E-step kernel sources: an ncu record only describes the build it was taken from."""
+ESTEP_SOURCES = ("estep.cuh", "devmath.cuh", "math_tables.h", "estep_inst.inc")
+
+
+def kernel_source_hash(names=ESTEP_SOURCES):
+    """sha256 over kernel sources: an ncu record only describes the build it was taken from."""
     import hashlib
     h = hashlib.sha256()
     src = os.path.join(ROOT, "oni_ml_b200", "csrc")
-    for name in ("estep.cuh", "devmath.cuh", "math_tables.h", "estep_inst.inc"):
+    for name in names:
         with open(os.path.join(src, name), "rb") as f:
             h.update(f.read())
     return h.hexdigest()[:16]
 
 
-def ncu_profile_record():
-    """profiles/estep_ncu.json (written by `profiles/summarize_ncu.py json <report>` from an
-    `ncu --set full` capture of bench.py): per-word-visit DRAM bytes and FP64 instruction count
-    of the main E-step launch.  None when absent or taken from other kernel sources."""
-    path = os.path.join(ROOT, "profiles", "estep_ncu.json")
+def ncu_profile_record(name="estep_ncu.json", sources=ESTEP_SOURCES):
+    """profiles/estep_ncu.json / score_ncu.json (written by `profiles/summarize_ncu.py json ...`
+    from an `ncu --set full` capture of bench.py): DRAM bytes and FP64 instruction count per unit
+    of work of the dominant launch.  None when absent or taken from other kernel sources."""
+    path = os.path.join(ROOT, "profiles", name)
     try:
         with open(path) as f:
             rec = json.load(f)
     except Exception:
         return None
-    if rec.get("source_hash") != kernel_source_hash():
+    if rec.get("source_hash") != kernel_source_hash(sources):
         return None
-    rec["file"] = "profiles/estep_ncu.json"
+    rec["file"] = "profiles/" + name
     return rec
 
 
@@ -661,21 +672,22 @@ def score_arm(args):
     return 0
 
 
-def _score_arm(args):
+def _score_arm(args, attached=False):
     """BASELINE configs[4]: flow events scored from theta [1M x 20] / p(w|z) [50k x 20],
-    threshold filter, ranked ascending.  One step = one pass over all events."""
+    threshold filter, ranked ascending.  One step = one pass over all events.
+    attached: called from the EM arm at N = 1 (no process group of its own)."""
     import torch
     import torch.distributed as dist
     from oni_ml_b200 import scoring
     from oracle import pyoracle
     rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
+    world = 1 if attached else int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    D, V, K, n = WORKLOAD["docs_per_gpu"], WORKLOAD["vocab"], K_TOPICS, args.events
+    D, V, K, n = 1_000_000, 50_000, 20, (args.scoring_events if attached else args.events)
     g = torch.Generator(device=dev); g.manual_seed(20160127)  # the tables: the same on every rank
     th = torch._standard_gamma(torch.full((D, K), 0.3, dtype=torch.float64, device=dev), generator=g) + 1e-300
     th /= th.sum(1, keepdim=True)
@@ -742,7 +754,11 @@ def _score_arm(args):
         surv_all = sum(int(x[2]) for x in allr)
     # e2e: host arrays through oni_score_flow (upload of 16 B/event inside); with several ranks the
     # ranked shares (at most 1M survivors each) are then gathered and merged on (key, global index)
-    hev = [a.cpu().pin_memory().numpy() for a in ev]
+    hev = []
+    for a in ev:  # pinned host copies of the event indices (what a caller keeps its day of events in)
+        h = torch.empty(a.shape, dtype=a.dtype, pin_memory=True)
+        h.copy_(a)
+        hev.append(h.numpy())
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -786,6 +802,7 @@ def _score_arm(args):
                      and np.array_equal(pre["key"].view(np.int64), ok[:mm].view(np.int64)))
     peak, peak_src = peaks()
     achieved = n * (16 + 16 * K + 8) / (statistics.mean(ms_score) * 1e-3) / 1e9
+    sprof = ncu_profile_record("score_ncu.json", ("scoring.cu", "radix_sort.cuh"))
     if world > 1:
         dist.destroy_process_group()
     return {
@@ -806,9 +823,12 @@ def _score_arm(args):
         "ms_per_rank": [round(x, 3) for x in per_rank_ms],
         "gpu_launches": int(launches), "clocks": clocks, "wall_ms_per_step": wall / args.steps * 1e3,
         "roofline": {"bound": "hbm", "kernel": "score_filter_paired_kernel<flow,10>", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": int(286.3 * n),
-                     "dram_frac": 286.3 * n / (statistics.mean(ms_score) * 1e-3) / 1e9 / peak,
-                     "traffic_source": "ncu dram__bytes_read per event (profiles/r1_score.txt) x events",
+                     "unit": "GB/s", "frac": achieved / peak,
+                     # DRAM bytes per event from the ncu report of the current scoring.cu (refused when stale)
+                     "traffic": int(sprof["dram_bytes_per_event"] * n) if sprof else None,
+                     "dram_frac": (sprof["dram_bytes_per_event"] * n / (statistics.mean(ms_score) * 1e-3) / 1e9 / peak) if sprof else None,
+                     "traffic_source": ("ncu dram__bytes per event (profiles/score_ncu.json) x events" if sprof else
+                                        "no ncu record of the current scoring.cu under profiles/ (stale ones are refused)"),
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": n * (16 + 16 * K + 8), "ms_per_launch": statistics.mean(ms_score)},
         "breakdown_ms": {"score_filter": statistics.mean(ms_score), "rank": statistics.mean(ms_sort)},
@@ -834,6 +854,8 @@ def main():
     ap.add_argument("--workload", default="em", choices=["em", "score"],
                     help="em (default, the headline metric) or score (BASELINE configs[4])")
     ap.add_argument("--events", type=int, default=250_000_000, help="events for --workload score")
+    ap.add_argument("--scoring-events", type=int, default=1_000_000_000,
+                    help="events of the scoring record attached to the default N = 1 line (BASELINE configs[4]: 10^9)")
     ap.add_argument("--doc-dist", default="uniform", choices=["uniform", "zipf"],
                     help="--workload score: how events pick their documents (zipf = Zipf(1.0), the locality variant)")
     ap.add_argument("--shape", default="flow_day", choices=sorted(SHAPES),

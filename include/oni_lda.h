@@ -285,6 +285,15 @@ int oni_score_begin(oni_score_ctx *ctx);
 int oni_score_events_device(oni_score_ctx *ctx, int32_t is_flow, int64_t num_events,
                             int64_t idx_base, const int32_t *a_doc, const int32_t *b_doc,
                             const int32_t *a_word, const int32_t *b_word, double tol);
+/* The same from HOST index arrays (what oni_score_flow / oni_score_dns run on a context of  */
+/* their own): the events go up in chunks on a copy stream while the previous chunk is scored, */
+/* so a caller that scores day after day against the same tables keeps ONE context and pays   */
+/* the table upload once.  Pinned arrays travel at PCIe speed, pageable ones slower.  An index */
+/* >= num_docs / num_terms fails with ONI_ERR_ARG (checked by the kernel; -1 = lookup miss ->  */
+/* the scripts' constant vector, flow_post_lda.scala:228-231).                                 */
+int oni_score_events_host(oni_score_ctx *ctx, int32_t is_flow, int64_t num_events, int64_t idx_base,
+                          const int32_t *a_doc, const int32_t *b_doc, const int32_t *a_word,
+                          const int32_t *b_word, double tol);
 /* Rank the survivors: ascending key, ties by event index. */
 int oni_score_rank(oni_score_ctx *ctx, int64_t *n_survivors);
 /* First `cap` ranked survivors to host arrays. */
@@ -294,6 +303,11 @@ int oni_score_fetch(oni_score_ctx *ctx, int64_t cap, int64_t *out_idx, double *o
 int oni_score_fetch_sides(oni_score_ctx *ctx, int32_t is_flow, int64_t cap, int64_t idx_base,
                           const int32_t *a_doc, const int32_t *b_doc, const int32_t *a_word,
                           const int32_t *b_word, double *out_a, double *out_b);
+/* The same when the events live in HOST arrays (any number of chunks): the index quadruples */
+/* of the `cap` ranked survivors are gathered on the host and scored once more.              */
+int oni_score_fetch_sides_host(oni_score_ctx *ctx, int32_t is_flow, int64_t cap, int64_t idx_base,
+                               const int32_t *a_doc, const int32_t *b_doc, const int32_t *a_word,
+                               const int32_t *b_word, double *out_a, double *out_b);
 /* CUDA-event times of the last run and kernels launched so far. */
 int oni_score_get_stats(oni_score_ctx *ctx, double *ms_score, double *ms_sort, int64_t *launches);
 

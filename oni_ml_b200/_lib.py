@@ -114,6 +114,8 @@ SIGNATURES = {
     "oni_score_rank": (C.c_int, [_vp, C.POINTER(_i64)]),
     "oni_score_fetch": (C.c_int, [_vp, _i64, _vp, _vp]),
     "oni_score_fetch_sides": (C.c_int, [_vp, _i32, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "oni_score_events_host": (C.c_int, [_vp, _i32, _i64, _i64, _vp, _vp, _vp, _vp, _f64]),
+    "oni_score_fetch_sides_host": (C.c_int, [_vp, _i32, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     "oni_score_get_stats": (C.c_int, [_vp, C.POINTER(_f64), C.POINTER(_f64), C.POINTER(_i64)]),
     "oni_score_flow_noalloc": (C.c_int, [_i32, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _f64, _i64,
                                          _vp, _vp, C.POINTER(_i64), _vp]),

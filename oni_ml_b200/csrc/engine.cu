@@ -870,25 +870,6 @@ extern "C" int oni_lda_get_logbeta(oni_lda_ctx *c, double *logbeta)
 {
     if (!c || !logbeta) return oni_set_error(ONI_ERR_ARG, "get_logbeta: null argument");
     ONI_CUDA(cudaSetDevice(c->device));
-    {
-        // exp(digamma(gamma) + log beta) must be a normal number for at least one topic of every
-        // word, or the unshifted E-step normalises garbage (the reference's log_sum chain,
-        // lda-inference.c:53-64, has no such limit): remember how low this model goes
-        const size_t V = (size_t)c->V;
-        std::vector<double> rowmax(V, -INFINITY);
-        double lo = INFINITY;
-        for (int k = 0; k < c->K; k++) {
-            const double *row = logbeta + (size_t)k * V;
-            for (size_t w = 0; w < V; w++) {
-                const double x = row[w];
-                if (x != x) return oni_set_error(ONI_ERR_ARG, "model: log beta[%d][%zu] is NaN", k, w);
-                rowmax[w] = x > rowmax[w] ? x : rowmax[w];
-                lo = x < lo ? x : lo;
-            }
-        }
-        c->model_min = lo;
-        c->model_min_rowmax = *std::min_element(rowmax.begin(), rowmax.end());
-    }
     double *stage = nullptr;
     ONI_TRY(dev_alloc(&stage, (size_t)c->K * c->V));
     const dim3 grid((c->V + 31) / 32, (c->K + 31) / 32), block(32, 8);

@@ -90,7 +90,7 @@ __host__ __device__ inline double key_value(unsigned long long u)
 
 template <bool FLOW>
 __global__ void __launch_bounds__(256)
-score_filter_kernel(int K, const double *__restrict__ theta, const double *__restrict__ pwz,
+score_filter_kernel(int K, int D, int V, const double *__restrict__ theta, const double *__restrict__ pwz,
                     long long n, const int32_t *__restrict__ a_doc, const int32_t *__restrict__ b_doc,
                     const int32_t *__restrict__ a_word, const int32_t *__restrict__ b_word,
                     double dflt, double tol, long long idx_base, unsigned long long *surv_key,
@@ -106,9 +106,15 @@ score_filter_kernel(int K, const double *__restrict__ theta, const double *__res
         bool keep = false;
         double key = 0.0;
         if (e < n) {
-            const double sa = side_score(theta, pwz, K, a_doc[e], a_word[e], dflt, vec2);
+            // an index beyond its table is the caller's error: flagged (counter[1]) and read as a miss
+            int32_t ad = a_doc[e], aw = a_word[e], bd = FLOW ? b_doc[e] : -1, bw = FLOW ? b_word[e] : -1;
+            if (ad >= D || aw >= V || bd >= D || bw >= V) {
+                counter[1] = 1;
+                ad = ad >= D ? -1 : ad; aw = aw >= V ? -1 : aw; bd = bd >= D ? -1 : bd; bw = bw >= V ? -1 : bw;
+            }
+            const double sa = side_score(theta, pwz, K, ad, aw, dflt, vec2);
             if (FLOW) {
-                const double sb = side_score(theta, pwz, K, b_doc[e], b_word[e], dflt, vec2);
+                const double sb = side_score(theta, pwz, K, bd, bw, dflt, vec2);
                 key = (sb < sa) ? sb : sa;  // flow_post_lda.scala:238
             } else {
                 key = sa;
@@ -191,7 +197,7 @@ __device__ __forceinline__ double dot_paired(const double *theta, const double *
 #endif
 template <bool FLOW, int CH>
 __global__ void __launch_bounds__(128, ONI_SCORE_MINB)
-score_filter_paired_kernel(const double *__restrict__ theta, const double *__restrict__ pwz, long long n,
+score_filter_paired_kernel(int D, int V, const double *__restrict__ theta, const double *__restrict__ pwz, long long n,
                            const int32_t *__restrict__ a_doc, const int32_t *__restrict__ b_doc,
                            const int32_t *__restrict__ a_word, const int32_t *__restrict__ b_word,
                            double dflt, double tol, long long idx_base, unsigned long long *surv_key,
@@ -203,16 +209,22 @@ score_filter_paired_kernel(const double *__restrict__ theta, const double *__res
     for (long long base = (long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += stride) {
         const long long e = base + lane;
         const bool in = e < n;
-        // lanes past the end take part in the exchange with "missing" rows
-        const double sa = dot_paired<CH>(theta, pwz, in ? a_doc[e] : -1, in ? a_word[e] : -1, dflt, lane);
+        // lanes past the end take part in the exchange with "missing" rows; an index beyond its
+        // table is the caller's error: flagged (counter[1]) and read as a miss
+        int32_t ad = in ? a_doc[e] : -1, aw = in ? a_word[e] : -1;
+        int32_t bd = (FLOW && in) ? b_doc[e] : -1, bw = (FLOW && in) ? b_word[e] : -1;
+        if (ad >= D || aw >= V || bd >= D || bw >= V) {
+            counter[1] = 1;
+            ad = ad >= D ? -1 : ad; aw = aw >= V ? -1 : aw; bd = bd >= D ? -1 : bd; bw = bw >= V ? -1 : bw;
+        }
+        const double sa = dot_paired<CH>(theta, pwz, ad, aw, dflt, lane);
         double key = sa;
         if (FLOW) {
             // (the second side's 2*CH loads must stay below the first side's sum: all 4*CH in
             //  flight at once need 192 registers and leave 8 warps per SM; the compiler hoists
             //  them over any barrier, so their addresses are made to depend on sa)
             const int order = (sa != sa) ? 1 : 0;  // always 0: makes the addresses below depend on sa
-            const double sb = dot_paired<CH>(theta, pwz, in ? b_doc[e] + order : -1, in ? b_word[e] + order : -1,
-                                             dflt, lane);
+            const double sb = dot_paired<CH>(theta, pwz, bd >= 0 ? bd + order : -1, bw >= 0 ? bw + order : -1, dflt, lane);
             key = (sb < sa) ? sb : sa;  // flow_post_lda.scala:238
         }
         const bool keep = in && (key < tol);  // strict, flow_post_lda.scala:245
@@ -248,7 +260,7 @@ __global__ void rescored_kernel(int K, const double *theta, const double *pwz, l
     const bool vec2 = (K % 2) == 0;
     for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < m;
          r += (long long)gridDim.x * blockDim.x) {
-        const long long e = (long long)idx[r] - idx_base;
+        const long long e = idx ? (long long)idx[r] - idx_base : r;  // (no list: the events ARE the ranked ones)
         out_a[r] = side_score(theta, pwz, K, a_doc[e], a_word[e], dflt, vec2);
         if (FLOW) out_b[r] = side_score(theta, pwz, K, b_doc[e], b_word[e], dflt, vec2);
     }
@@ -307,6 +319,11 @@ struct oni_score_ctx {
     double *d_theta = nullptr, *d_pwz = nullptr;
     unsigned long long *d_counter = nullptr, *d_totals = nullptr;
     DevBuf key[2], idx[2], counts, ev[4], out_a, out_b;
+    // events from host arrays: three sets of chunk buffers, uploads on a stream of their own so
+    // that chunk i+1 travels while chunk i is scored
+    cudaStream_t copy_stream = nullptr;
+    DevBuf up[2][4];
+    cudaEvent_t up_done[2] = {};
     unsigned long long cap = 0;     // survivor capacity (entries)
     unsigned long long n_surv = 0;  // survivors of the last run
     int cur = 0;                    // which ping-pong buffer holds the ranked list
@@ -338,10 +355,14 @@ extern "C" int oni_score_create(int32_t device, int32_t K, int32_t D, int32_t V,
         ONI_CUDA(cudaEventCreate(&c->e0)); ONI_CUDA(cudaEventCreate(&c->e1)); ONI_CUDA(cudaEventCreate(&c->e2));
         ONI_CUDA(cudaMalloc((void **)&c->d_theta, sizeof(double) * std::max<size_t>(1, (size_t)D * K)));
         ONI_CUDA(cudaMalloc((void **)&c->d_pwz, sizeof(double) * std::max<size_t>(1, (size_t)V * K)));
-        ONI_CUDA(cudaMalloc((void **)&c->d_counter, sizeof(unsigned long long)));
+        ONI_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; b++) ONI_CUDA(cudaEventCreateWithFlags(&c->up_done[b], cudaEventDisableTiming));
+        ONI_CUDA(cudaMalloc((void **)&c->d_counter, 2 * sizeof(unsigned long long)));  // [0] survivors, [1] bad-index flag
         ONI_CUDA(cudaMalloc((void **)&c->d_totals, sizeof(unsigned long long) * RS_MAX_PASSES * 256));
-        ONI_CUDA(cudaMemcpy(c->d_theta, theta, sizeof(double) * (size_t)D * K, cudaMemcpyHostToDevice));
-        ONI_CUDA(cudaMemcpy(c->d_pwz, pwz, sizeof(double) * (size_t)V * K, cudaMemcpyHostToDevice));
+        ONI_CUDA(cudaMemsetAsync(c->d_counter, 0, 2 * sizeof(unsigned long long), c->stream));
+        ONI_CUDA(cudaMemcpyAsync(c->d_theta, theta, sizeof(double) * (size_t)D * K, cudaMemcpyHostToDevice, c->stream));
+        ONI_CUDA(cudaMemcpyAsync(c->d_pwz, pwz, sizeof(double) * (size_t)V * K, cudaMemcpyHostToDevice, c->stream));
+        ONI_CUDA(cudaStreamSynchronize(c->stream));  // (the caller's arrays may go away)
         return ONI_OK;
     };
     const int rc = build();
@@ -359,6 +380,9 @@ extern "C" void oni_score_destroy(oni_score_ctx *c)
     for (auto &b : c->idx) b.release();
     for (auto &b : c->ev) b.release();
     c->counts.release(); c->out_a.release(); c->out_b.release();
+    for (auto &set : c->up) for (auto &b : set) b.release();
+    for (auto &e : c->up_done) if (e) cudaEventDestroy(e);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->e0) cudaEventDestroy(c->e0);
     if (c->e1) cudaEventDestroy(c->e1);
     if (c->e2) cudaEventDestroy(c->e2);
@@ -372,7 +396,8 @@ static int reserve_survivors(oni_score_ctx *c, unsigned long long cap)
     // growing keeps what is already there (chunked runs append across calls)
     for (int b = 0; b < 2; b++) {
         DevBuf nk, ni;
-        ONI_TRY(nk.reserve(cap * 8)); ONI_TRY(ni.reserve(cap * 8));
+        ONI_TRY(nk.reserve(cap * 8));
+        { const int rc = ni.reserve(cap * 8); if (rc != ONI_OK) { nk.release(); return rc; } }
         if (c->cap && b == c->cur) {
             ONI_CUDA(cudaMemcpyAsync(nk.p, c->key[b].p, c->cap * 8, cudaMemcpyDeviceToDevice, c->stream));
             ONI_CUDA(cudaMemcpyAsync(ni.p, c->idx[b].p, c->cap * 8, cudaMemcpyDeviceToDevice, c->stream));
@@ -390,7 +415,7 @@ extern "C" int oni_score_begin(oni_score_ctx *c)
 {
     if (!c) return oni_set_error(ONI_ERR_ARG, "score_begin: null context");
     ONI_CUDA(cudaSetDevice(c->device));
-    ONI_CUDA(cudaMemsetAsync(c->d_counter, 0, sizeof(unsigned long long), c->stream));
+    ONI_CUDA(cudaMemsetAsync(c->d_counter, 0, 2 * sizeof(unsigned long long), c->stream));
     c->n_surv = 0; c->cur = 0; c->ms_score = c->ms_sort = 0;
     return ONI_OK;
 }
@@ -417,21 +442,25 @@ extern "C" int oni_score_events_device(oni_score_ctx *c, int32_t is_flow, int64_
         const int pblocks = (int)std::min<long long>((n + 127) / 128, (long long)c->sm_count * 32);
         if (paired && is_flow)
             score_filter_paired_kernel<true, 10><<<pblocks, 128, 0, c->stream>>>(
-                c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
+                c->D, c->V, c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         else if (paired)
             score_filter_paired_kernel<false, 10><<<pblocks, 128, 0, c->stream>>>(
-                c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
+                c->D, c->V, c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         else if (is_flow)
             score_filter_kernel<true><<<blocks, 256, 0, c->stream>>>(
-                c->K, c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
+                c->K, c->D, c->V, c->d_theta, c->d_pwz, n, a_doc, b_doc, a_word, b_word, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         else
             score_filter_kernel<false><<<blocks, 256, 0, c->stream>>>(
-                c->K, c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
+                c->K, c->D, c->V, c->d_theta, c->d_pwz, n, a_doc, nullptr, a_word, nullptr, dflt, tol, idx_base, sk, si, c->cap, c->d_counter);
         c->launches++;
         ONI_CUDA(cudaEventRecord(c->e1, c->stream));
-        unsigned long long total = 0;
-        ONI_CUDA(cudaMemcpyAsync(&total, c->d_counter, sizeof total, cudaMemcpyDeviceToHost, c->stream));
+        unsigned long long two[2] = {0, 0};
+        ONI_CUDA(cudaMemcpyAsync(two, c->d_counter, sizeof two, cudaMemcpyDeviceToHost, c->stream));
         ONI_CUDA(cudaStreamSynchronize(c->stream));
+        const unsigned long long total = two[0];
+        if (two[1])
+            return oni_set_error(ONI_ERR_ARG, "score: an event's document index is >= %d or its word index >= %d "
+                                 "(events %lld..%lld)", c->D, c->V, (long long)idx_base, (long long)(idx_base + n - 1));
         float ms = 0;
         cudaEventElapsedTime(&ms, c->e0, c->e1);
         if (total <= c->cap) { c->n_surv = total; c->ms_score += ms; return ONI_OK; }
@@ -527,6 +556,98 @@ extern "C" int oni_score_get_stats(oni_score_ctx *c, double *ms_score, double *m
 }
 
 // ------------------------------------------------------ host-buffer entry points
+// Score n events whose indices are in HOST arrays; survivors accumulate as with
+// oni_score_events_device.  The events travel in chunks (2^24 by default, ONI_SCORE_CHUNK) through
+// two sets of device buffers on a copy stream of their own, so that chunk i+1 is on the bus while
+// chunk i is scored: with pinned host arrays a day of events costs its PCIe time (16 bytes per
+// flow event) and little more.  Pageable arrays work, at the speed of staged copies.
+extern "C" int oni_score_events_host(oni_score_ctx *c, int32_t is_flow, int64_t n, int64_t idx_base,
+                                     const int32_t *a_doc, const int32_t *b_doc, const int32_t *a_word,
+                                     const int32_t *b_word, double tol)
+{
+    if (!c || n < 0 || (n > 0 && (!a_doc || !a_word || (is_flow && (!b_doc || !b_word)))))
+        return oni_set_error(ONI_ERR_ARG, "score_events_host: bad argument");
+    if (n == 0) return ONI_OK;
+    ONI_CUDA(cudaSetDevice(c->device));
+    const int nsrc = is_flow ? 4 : 2;
+    const int32_t *src[4] = {a_doc, a_word, b_doc, b_word};
+    const char *env = getenv("ONI_SCORE_CHUNK");
+    int64_t chunk = env ? atoll(env) : ((int64_t)1 << 24);
+    if (chunk < 1) chunk = 1;
+    chunk = std::min(chunk, n);
+    const int64_t nchunks = (n + chunk - 1) / chunk;
+    for (int b = 0; b < (nchunks > 1 ? 2 : 1); b++)
+        for (int q = 0; q < nsrc; q++) ONI_TRY(c->up[b][q].reserve(sizeof(int32_t) * (size_t)chunk));
+    // (the buffers may still be read by a kernel of an earlier call on this context)
+    ONI_CUDA(cudaStreamSynchronize(c->stream));
+    auto upload = [&](int64_t i) -> int {
+        const int b = (int)(i & 1);
+        const int64_t lo = i * chunk, m = std::min(chunk, n - lo);
+        for (int q = 0; q < nsrc; q++)
+            ONI_CUDA(cudaMemcpyAsync(c->up[b][q].p, src[q] + lo, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice,
+                                     c->copy_stream));
+        ONI_CUDA(cudaEventRecord(c->up_done[b], c->copy_stream));
+        return ONI_OK;
+    };
+    ONI_TRY(upload(0));
+    for (int64_t i = 0; i < nchunks; i++) {
+        // chunk i+1 goes into the buffers of chunk i-1, whose kernel has finished (every chunk ends
+        // with a read-back of the survivor count)
+        if (i + 1 < nchunks) ONI_TRY(upload(i + 1));
+        const int b = (int)(i & 1);
+        const int64_t lo = i * chunk, m = std::min(chunk, n - lo);
+        ONI_CUDA(cudaStreamWaitEvent(c->stream, c->up_done[b], 0));
+        const int rc = oni_score_events_device(c, is_flow, m, idx_base + lo, (int32_t *)c->up[b][0].p,
+                                               (int32_t *)c->up[b][2].p, (int32_t *)c->up[b][1].p,
+                                               (int32_t *)c->up[b][3].p, tol);
+        if (rc != ONI_OK) { cudaStreamSynchronize(c->copy_stream); return rc; }
+    }
+    return ONI_OK;
+}
+
+// src/dst scores of the first `cap` ranked survivors of events that live in HOST arrays: their
+// index quadruples are gathered on the host (cap entries, however many chunks the events took),
+// uploaded, and scored once more in ranked order.
+extern "C" int oni_score_fetch_sides_host(oni_score_ctx *c, int32_t is_flow, int64_t cap, int64_t idx_base,
+                                          const int32_t *a_doc, const int32_t *b_doc, const int32_t *a_word,
+                                          const int32_t *b_word, double *out_a, double *out_b)
+{
+    if (!c || cap < 0 || !a_doc || !a_word || (is_flow && (!b_doc || !b_word)))
+        return oni_set_error(ONI_ERR_ARG, "score_fetch_sides_host: bad argument");
+    ONI_CUDA(cudaSetDevice(c->device));
+    const size_t m = (size_t)std::min<unsigned long long>((unsigned long long)cap, c->n_surv);
+    if (m == 0) return ONI_OK;
+    std::vector<int64_t> idx(m);
+    ONI_CUDA(cudaMemcpy(idx.data(), c->idx[c->cur].p, sizeof(int64_t) * m, cudaMemcpyDeviceToHost));
+    const int nsrc = is_flow ? 4 : 2;
+    const int32_t *src[4] = {a_doc, a_word, b_doc, b_word};
+    std::vector<int32_t> g[4];
+    for (int q = 0; q < nsrc; q++) {
+        g[q].resize(m);
+        for (size_t r = 0; r < m; r++) g[q][r] = src[q][idx[r] - idx_base];
+        ONI_TRY(c->ev[q].reserve(sizeof(int32_t) * m));
+        ONI_CUDA(cudaMemcpyAsync(c->ev[q].p, g[q].data(), sizeof(int32_t) * m, cudaMemcpyHostToDevice, c->stream));
+    }
+    ONI_TRY(c->out_a.reserve(sizeof(double) * m));
+    ONI_TRY(c->out_b.reserve(sizeof(double) * m));
+    const double dflt = is_flow ? 0.05 : 0.1;
+    const int blocks = (int)std::min<long long>(((long long)m + 255) / 256, 4096);
+    if (is_flow)
+        rescored_kernel<true><<<blocks, 256, 0, c->stream>>>(c->K, c->d_theta, c->d_pwz, (long long)m, nullptr, 0,
+            (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p, (int32_t *)c->ev[1].p, (int32_t *)c->ev[3].p, dflt,
+            (double *)c->out_a.p, (double *)c->out_b.p);
+    else
+        rescored_kernel<false><<<blocks, 256, 0, c->stream>>>(c->K, c->d_theta, c->d_pwz, (long long)m, nullptr, 0,
+            (int32_t *)c->ev[0].p, nullptr, (int32_t *)c->ev[1].p, nullptr, dflt,
+            (double *)c->out_a.p, (double *)c->out_b.p);
+    c->launches++;
+    ONI_CUDA(cudaStreamSynchronize(c->stream));  // (the gathered vectors die at return)
+    ONI_CUDA(cudaGetLastError());
+    if (out_a) ONI_CUDA(cudaMemcpy(out_a, c->out_a.p, sizeof(double) * m, cudaMemcpyDeviceToHost));
+    if (out_b && is_flow) ONI_CUDA(cudaMemcpy(out_b, c->out_b.p, sizeof(double) * m, cudaMemcpyDeviceToHost));
+    return ONI_OK;
+}
+
 static int score_host(int32_t device, int is_flow, int32_t K, int32_t D, int32_t V, const double *theta,
                       const double *pwz, int64_t n, const int32_t *a_doc, const int32_t *b_doc,
                       const int32_t *a_word, const int32_t *b_word, double tol, int64_t out_cap,
@@ -536,40 +657,14 @@ static int score_host(int32_t device, int is_flow, int32_t K, int32_t D, int32_t
     if (n < 0 || out_cap < 0 || !theta || !pwz) return oni_set_error(ONI_ERR_ARG, "score: bad argument");
     oni_score_ctx *c = nullptr;
     ONI_TRY(oni_score_create(device, K, D, V, theta, pwz, &c));
-    int rc = ONI_OK;
-    const int nsrc = is_flow ? 4 : 2;
-    const int32_t *src[4] = {a_doc, a_word, b_doc, b_word};
-    // validate indices on the host: the kernels trust them
-    for (int q = 0; q < nsrc && rc == ONI_OK; q++) {
-        const int32_t lim = (q % 2 == 0) ? D : V;
-        for (int64_t e = 0; e < n; e++)
-            if (src[q][e] >= lim) { rc = oni_set_error(ONI_ERR_ARG, "score: index %d >= %d at event %lld", src[q][e], lim, (long long)e); break; }
-    }
-    // events go up in one piece when they fit (16 B/event flow); chunking keeps
-    // the device footprint bounded for billion-event days
-    const int64_t chunk = std::min<int64_t>(n, (int64_t)1 << 28);
-    if (rc == ONI_OK) rc = oni_score_begin(c);
-    for (int q = 0; q < nsrc && rc == ONI_OK; q++) rc = c->ev[q].reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(chunk, 1));
-    for (int64_t lo = 0; lo < n && rc == ONI_OK; lo += chunk) {
-        const int64_t m = std::min(chunk, n - lo);
-        for (int q = 0; q < nsrc && rc == ONI_OK; q++)
-            if (cudaMemcpyAsync(c->ev[q].p, src[q] + lo, sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, c->stream) != cudaSuccess)
-                rc = oni_set_error(ONI_ERR_CUDA, "score: event upload failed");
-        if (rc == ONI_OK)
-            rc = oni_score_events_device(c, is_flow, m, base + lo, (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p,
-                                         (int32_t *)c->ev[1].p, (int32_t *)c->ev[3].p, tol);
-    }
+    int rc = oni_score_begin(c);
+    // (indices are range-checked by the scoring kernel itself; -1 = lookup miss)
+    if (rc == ONI_OK) rc = oni_score_events_host(c, is_flow, n, base, a_doc, b_doc, a_word, b_word, tol);
     int64_t total = 0;
     if (rc == ONI_OK) rc = oni_score_rank(c, &total);
     if (rc == ONI_OK) rc = oni_score_fetch(c, out_cap, out_idx, out_key);
-    if (rc == ONI_OK && (out_a || out_b)) {
-        if (chunk == n) {
-            rc = oni_score_fetch_sides(c, is_flow, out_cap, base, (int32_t *)c->ev[0].p, (int32_t *)c->ev[2].p,
-                                       (int32_t *)c->ev[1].p, (int32_t *)c->ev[3].p, out_a, out_b);
-        } else {
-            rc = oni_set_error(ONI_ERR_ARG, "score: per-side scores need the events in one chunk (n <= 2^28)");
-        }
-    }
+    if (rc == ONI_OK && (out_a || out_b) && n > 0)
+        rc = oni_score_fetch_sides_host(c, is_flow, out_cap, base, a_doc, b_doc, a_word, b_word, out_a, out_b);
     if (out_n) *out_n = total;
     oni_score_destroy(c);
     return rc;
@@ -824,7 +919,8 @@ extern "C" int oni_score_flow_noalloc(int32_t device, int32_t K, const double *d
     int sms = 0;
     ONI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     const int blocks = (int)std::min<long long>((n + 255) / 256, (long long)sms * 16);
-    score_filter_kernel<true><<<blocks, 256, 0, s>>>(K, d_theta, d_pwz, n, d_src_doc, d_dst_doc, d_src_word,
+    // (this entry point is not told the table sizes: no index is "beyond" them, as before)
+    score_filter_kernel<true><<<blocks, 256, 0, s>>>(K, 0x7fffffff, 0x7fffffff, d_theta, d_pwz, n, d_src_doc, d_dst_doc, d_src_word,
                                                      d_dst_word, 0.05, tol, 0, key[0], idx[0],
                                                      NA_MAX_SURVIVORS, counter);
     unsigned long long total = 0;

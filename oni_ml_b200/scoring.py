@@ -92,6 +92,18 @@ class ScoreContext:
         check(self._L.oni_score_events_device(self._h, 0, int(doc.numel()), idx_base, ptr(doc), None,
                                               ptr(word), None, float(tol)))
 
+    def score_flow_host(self, src_doc, dst_doc, src_word, dst_word, tol: float, idx_base: int = 0):
+        """Events in host arrays (numpy int32; pinned memory travels at PCIe speed): uploaded in
+        chunks while the previous chunk is scored (oni_score_events_host)."""
+        a = [np.ascontiguousarray(x, dtype=np.int32) for x in (src_doc, dst_doc, src_word, dst_word)]
+        check(self._L.oni_score_events_host(self._h, 1, int(a[0].shape[0]), idx_base, ptr(a[0]), ptr(a[1]),
+                                            ptr(a[2]), ptr(a[3]), float(tol)))
+
+    def score_dns_host(self, doc, word, tol: float, idx_base: int = 0):
+        a = [np.ascontiguousarray(x, dtype=np.int32) for x in (doc, word)]
+        check(self._L.oni_score_events_host(self._h, 0, int(a[0].shape[0]), idx_base, ptr(a[0]), None,
+                                            ptr(a[1]), None, float(tol)))
+
     def rank(self) -> int:
         n = C.c_int64()
         check(self._L.oni_score_rank(self._h, C.byref(n)))

@@ -3,6 +3,7 @@
 
   python profiles/summarize_ncu.py launches <launches.csv>
   python profiles/summarize_ncu.py raw <report.ncu-rep>      (needs ncu on PATH)
+  python profiles/summarize_ncu.py json-score <report.ncu-rep> <events of the profiled launch>   -> profiles/score_ncu.json
   python profiles/summarize_ncu.py json <report.ncu-rep> <word visits of the profiled launch> [kernel substring]
       -> profiles/estep_ncu.json: what bench.py's roofline record reads (DRAM bytes and FP64
          lane-operations per word visit of the main E-step launch), stamped with a hash of the
@@ -67,13 +68,40 @@ def raw(path):
         print("   stalls per issue: " + ", ".join("%s %.2f" % (n, x) for x, n in sorted(stalls, reverse=True)[:6]))
 
 
-def source_hash():
+def source_hash(names=("estep.cuh", "devmath.cuh", "math_tables.h", "estep_inst.inc")):  # = bench.py kernel_source_hash()
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     h = hashlib.sha256()
-    for name in ("estep.cuh", "devmath.cuh", "math_tables.h", "estep_inst.inc"):  # = bench.py kernel_source_hash()
+    for name in names:
         with open(os.path.join(root, "oni_ml_b200", "csrc", name), "rb") as f:
             h.update(f.read())
     return h.hexdigest()[:16]
+
+
+def to_json_score(path, events, kernel="score_filter_paired_kernel"):
+    """profiles/score_ncu.json: DRAM bytes per event of the scoring launch."""
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], dict(zip(rows[0], rows[1]))
+    pick = [dict(zip(hdr, r)) for r in rows[2:] if kernel in dict(zip(hdr, r)).get("Kernel Name", "")]
+    if len(pick) != 1:
+        raise SystemExit("%d launches match %r in %s; capture exactly one" % (len(pick), kernel, path))
+    d = pick[0]
+
+    def val(name):
+        v = float(d[name].replace(",", ""))
+        return v * {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "byte": 1.0,
+                    "ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(units[name], 1.0)
+    dram = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
+    rec = {"kernel": d["Kernel Name"], "report": os.path.basename(path),
+           "source_hash": source_hash(("scoring.cu", "radix_sort.cuh")), "launch_events": events,
+           "duration_ms": val("gpu__time_duration.sum"), "dram_bytes": dram, "dram_bytes_per_event": dram / events,
+           "dram_pct_of_peak": float(d["gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"]),
+           "l2_hit_pct": float(d["lts__t_sector_hit_rate.pct"]), "registers": int(d["launch__registers_per_thread"])}
+    dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "score_ncu.json")
+    with open(dst, "w") as f:
+        json.dump(rec, f, indent=1)
+        f.write("\n")
+    print(json.dumps(rec, indent=1))
 
 
 def to_json(path, visits, kernel="estep_kernel<4, 5"):
@@ -127,5 +155,7 @@ def to_json(path, visits, kernel="estep_kernel<4, 5"):
 if __name__ == "__main__":
     if sys.argv[1] == "json":
         to_json(sys.argv[2], float(sys.argv[3]), *sys.argv[4:5])
+    elif sys.argv[1] == "json-score":
+        to_json_score(sys.argv[2], float(sys.argv[3]), *sys.argv[4:5])
     else:
         {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2])

@@ -111,6 +111,64 @@ def test_long_document_paths_match_oracle(monkeypatch, k, alpha):
     assert lik2 > lik and launches > 0
 
 
+def test_long_document_leaves_the_digamma_table(monkeypatch):
+    """The long-document kernel tabulates the reference's digamma on [2^-8, 2^23); a document
+    whose gamma leaves that range (here: counts of ~10^6 on 200 pairs, gamma up to ~10^8) is run
+    again with the series itself.  Both long documents (one inside the table, one outside) and
+    the short ones beside them must match the oracle."""
+    monkeypatch.setenv("ONI_LDA_LONG_DOC", "64")
+    monkeypatch.setenv("ONI_LDA_EXCL_DOC", "150")
+    rng = np.random.default_rng(5)
+    V, k, alpha = 300, 20, 0.7
+    lens = [200, 120, 90] + rng.integers(1, 40, 60).tolist()
+    ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    word = rng.integers(0, V, int(ptr[-1])).astype(np.int32)
+    word[200:200 + V] = np.arange(V, dtype=np.int32)[: int(ptr[-1]) - 200][:V] % V
+    count = rng.geometric(0.3, int(ptr[-1])).astype(np.int32)
+    count[:200] = rng.integers(500_000, 2_000_000, 200).astype(np.int32)  # the first document
+    c = Corpus(ptr, word, count, V)
+    st = _lib.Settings(20, 1e-6, 20, 1e-6, 1)
+    with lda.LdaEngine(0, k, V, st) as eng:
+        eng.set_corpus(c)
+        eng.init_random(7, alpha)
+        lb0 = eng.logbeta()
+        ref = pyoracle.e_step(c, k, alpha, lb0, 20, 1e-6)
+        lik, _ = eng.em_iteration()
+        gam, it1 = eng.gamma(), eng.doc_iters()
+        s = eng.stats()
+    assert s["docs_exclusive"] == 1 and s["docs_long"] == 2
+    assert gam[0].max() > 2.0 ** 23  # the case the test is about
+    assert rel_err(gam, ref["gamma"]) < 1e-9
+    assert abs(lik - ref["lik"]) / abs(ref["lik"]) < 1e-11
+    assert int((np.diff(ptr) * it1).sum()) == ref["word_visits"]
+
+
+def test_loaded_model_with_an_underflowing_word(c0_corpus):
+    """A model that did not come from this engine's M-step (set_model / `lda inf` / a model-root
+    start) may hold a word whose every topic sits far below the -100 floor.  exp(digamma + log
+    beta) then underflows for all topics at once; the reference's log_sum chain
+    (lda-inference.c:53-64) still normalises it, and so must the engine (it picks the
+    max-shifted kernel from the model, not from alpha alone)."""
+    k, alpha = 20, 2.5
+    st = _lib.Settings(20, 1e-6, 20, 1e-6, 1)
+    rng = np.random.default_rng(3)
+    with lda.LdaEngine(0, k, c0_corpus.num_terms, st) as eng:
+        eng.set_corpus(c0_corpus)
+        eng.init_random(42, alpha)
+        lb0 = eng.logbeta()
+        used = np.unique(c0_corpus.word)
+        for w in used[:: max(1, len(used) // 7)]:
+            lb0[:, w] = -700.0 - 40.0 * rng.random(k)   # every topic of these words underflows
+        eng.set_model(lb0, alpha)
+        ref = pyoracle.e_step(c0_corpus, k, alpha, lb0, 20, 1e-6)
+        eng.e_step()
+        lik, _ = eng.m_step()
+        gam = eng.gamma()
+    assert np.isfinite(lik)
+    assert rel_err(gam, ref["gamma"]) < 1e-9
+    assert abs(lik - ref["lik"]) / abs(ref["lik"]) < 1e-11
+
+
 def _check_against_golden(d, r, k, v, names):
     if "likelihood.dat" in names:
         want = files.read_likelihood(os.path.join(d, "likelihood.dat"))
