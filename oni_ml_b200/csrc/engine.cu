@@ -423,8 +423,11 @@ extern "C" int oni_lda_create(int32_t device, int32_t K, int32_t V, const oni_ld
     int G, T;
     if (!pick_config(K, &G, &T))
         return oni_set_error(ONI_ERR_ARG, "num_topics=%d not supported (1..256)", K);
-    if (st->var_max_iter == 0)
-        return oni_set_error(ONI_ERR_ARG, "var max iter 0 is not supported (use -1 for no cap)");
+    // (the reference runs ZERO sweeps for 0 and for anything below -1 and then reports a bound of
+    //  0 -- lda-inference.c:46-47; that is a bug there, refused here)
+    if (st->var_max_iter == 0 || st->var_max_iter < -1)
+        return oni_set_error(ONI_ERR_ARG, "var max iter %d is not supported (a positive cap, or -1 for none)",
+                             st->var_max_iter);
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return oni_set_error(ONI_ERR_CUDA, "no CUDA device: this engine has no CPU path");
@@ -588,6 +591,7 @@ static int upload_model(oni_lda_ctx *c, const double *logbeta, double alpha)
         c->launches++;
         e = cudaMemcpyAsync(c->d_alpha, &alpha, sizeof(double), cudaMemcpyHostToDevice, c->stream);
     }
+    if (e == cudaSuccess) e = cudaMemsetAsync(c->d_nan, 0, sizeof(int32_t), c->stream);  // a new model, a clean slate
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     if (e == cudaSuccess) e = cudaGetLastError();
     cudaFree(stage);
@@ -827,12 +831,17 @@ static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
     if (cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]) == cudaSuccess) c->stats.ms_suffstats = ms;
     if (cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]) == cudaSuccess) c->stats.ms_mstep = ms;
     c->stats.kernel_launches = c->launches;
-    if (nan_flag || lik != lik)
+    if (nan_flag || lik != lik) {
+        cudaMemsetAsync(c->d_nan, 0, sizeof(int32_t), c->stream);  // reported once; the handle stays usable
         return oni_set_error(ONI_ERR_NAN, "a document bound is NaN (EM iteration %d)", c->em_iter + 1);
+    }
     // lda-estimate.c:260-262
     c->em_iter++;
     c->converged = (c->lik_old - lik) / c->lik_old;
-    if (c->converged < 0 && c->var_max_iter > 0) c->var_max_iter *= 2;
+    // lda-estimate.c:261 doubles on every decrease of the bound, -1 included (-1 -> -2 = zero sweeps
+    // from then on) and without an overflow guard; here "no cap" stays "no cap" and the doubling
+    // stops at 2^30
+    if (c->converged < 0 && c->var_max_iter > 0 && c->var_max_iter < (1 << 30)) c->var_max_iter *= 2;
     c->lik_old = lik;
     c->estep_done = false;
     if (likelihood) *likelihood = lik;

@@ -200,6 +200,9 @@ int run_inf(int argc, char **argv)
     std::vector<double> lik((size_t)corpus.num_docs), gamma((size_t)corpus.num_docs * K);
     if (rc == ONI_OK) rc = oni_lda_get_doc_likelihood(ctx, lik.data());
     if (rc == ONI_OK) rc = oni_lda_get_gamma(ctx, gamma.data());
+    // assert(!isnan(likelihood)), lda-inference.c:78: the reference aborts, this returns ONI_ERR_NAN
+    for (int d = 0; rc == ONI_OK && d < corpus.num_docs; d++)
+        if (lik[d] != lik[d]) rc = oni_set_error(ONI_ERR_NAN, "the bound of document %d is NaN", d);
     if (rc == ONI_OK) {
         std::string name = std::string(argv[5]) + "-lda-lhood.dat";  // lda-estimate.c:374-375
         FILE *f = fopen(name.c_str(), "w");

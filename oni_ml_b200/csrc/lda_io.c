@@ -128,14 +128,18 @@ static void *parse_lines(void *arg)
         p = q;
         if (pc->ndocs == pc->cap_docs) {
             pc->cap_docs = pc->cap_docs ? pc->cap_docs * 2 : 4096;
-            pc->len = realloc(pc->len, sizeof(int64_t) * pc->cap_docs);
+            void *nl = realloc(pc->len, sizeof(int64_t) * pc->cap_docs);
+            if (!nl) { pc->ok = 0; return NULL; }  /* (the old block stays owned by pc and is freed by the caller) */
+            pc->len = nl;
         }
         if (pc->npairs + (size_t)n > pc->cap_pairs) {
             while (pc->npairs + (size_t)n > pc->cap_pairs) pc->cap_pairs = pc->cap_pairs ? pc->cap_pairs * 2 : 65536;
-            pc->word = realloc(pc->word, sizeof(int32_t) * pc->cap_pairs);
-            pc->count = realloc(pc->count, sizeof(int32_t) * pc->cap_pairs);
+            void *nw = realloc(pc->word, sizeof(int32_t) * pc->cap_pairs);
+            if (nw) pc->word = nw;
+            void *nc = realloc(pc->count, sizeof(int32_t) * pc->cap_pairs);
+            if (nc) pc->count = nc;
+            if (!nw || !nc) { pc->ok = 0; return NULL; }
         }
-        if (!pc->len || !pc->word || !pc->count) { pc->ok = 0; return NULL; }
         for (long long i = 0; i < n; i++) {
             long long w, c;
             while (*p == ' ' || *p == '\t') p++;

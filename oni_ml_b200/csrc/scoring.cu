@@ -800,27 +800,30 @@ extern "C" int oni_lda_post(int32_t device, int32_t D, int32_t K, int32_t V, con
             a[i] = strtod(buf, nullptr);
         }
     };
-    if (gamma && theta && D > 0) {
-        DevBuf g, t;
-        ONI_TRY(g.reserve(sizeof(double) * (size_t)D * K)); ONI_TRY(t.reserve(sizeof(double) * (size_t)D * K));
-        ONI_CUDA(cudaMemcpy(g.p, gamma, sizeof(double) * (size_t)D * K, cudaMemcpyHostToDevice));
-        theta_kernel<<<std::min(4096, (D + 127) / 128), 128>>>(D, K, (double *)g.p, (double *)t.p);
-        ONI_CUDA(cudaMemcpy(theta, t.p, sizeof(double) * (size_t)D * K, cudaMemcpyDeviceToHost));
-        g.release(); t.release();
-        roundtrip(theta, (size_t)D * K);
-    }
-    if (logbeta && pwz && V > 0) {
-        DevBuf b, r, p;
-        ONI_TRY(b.reserve(sizeof(double) * (size_t)V * K)); ONI_TRY(r.reserve(sizeof(double) * (size_t)V * K));
-        ONI_TRY(p.reserve(sizeof(double) * (size_t)V * K));
-        ONI_CUDA(cudaMemcpy(b.p, logbeta, sizeof(double) * (size_t)V * K, cudaMemcpyHostToDevice));
-        pwz_kernel<<<K, 256>>>(K, V, (double *)b.p, (double *)r.p, (double *)p.p);
-        ONI_CUDA(cudaMemcpy(pwz, p.p, sizeof(double) * (size_t)V * K, cudaMemcpyDeviceToHost));
-        b.release(); r.release(); p.release();
-        roundtrip(pwz, (size_t)V * K);
-    }
-    ONI_CUDA(cudaGetLastError());
-    return ONI_OK;
+    DevBuf buf[3];  // released on every way out
+    auto run = [&]() -> int {
+        if (gamma && theta && D > 0) {
+            const size_t bytes = sizeof(double) * (size_t)D * K;
+            ONI_TRY(buf[0].reserve(bytes)); ONI_TRY(buf[1].reserve(bytes));
+            ONI_CUDA(cudaMemcpy(buf[0].p, gamma, bytes, cudaMemcpyHostToDevice));
+            theta_kernel<<<std::min(4096, (D + 127) / 128), 128>>>(D, K, (double *)buf[0].p, (double *)buf[1].p);
+            ONI_CUDA(cudaMemcpy(theta, buf[1].p, bytes, cudaMemcpyDeviceToHost));
+            roundtrip(theta, (size_t)D * K);
+        }
+        if (logbeta && pwz && V > 0) {
+            const size_t bytes = sizeof(double) * (size_t)V * K;
+            ONI_TRY(buf[0].reserve(bytes)); ONI_TRY(buf[1].reserve(bytes)); ONI_TRY(buf[2].reserve(bytes));
+            ONI_CUDA(cudaMemcpy(buf[0].p, logbeta, bytes, cudaMemcpyHostToDevice));
+            pwz_kernel<<<K, 256>>>(K, V, (double *)buf[0].p, (double *)buf[1].p, (double *)buf[2].p);
+            ONI_CUDA(cudaMemcpy(pwz, buf[2].p, bytes, cudaMemcpyDeviceToHost));
+            roundtrip(pwz, (size_t)V * K);
+        }
+        ONI_CUDA(cudaGetLastError());
+        return ONI_OK;
+    };
+    const int rc = run();
+    for (auto &b : buf) b.release();
+    return rc;
 }
 
 // ============================================================================

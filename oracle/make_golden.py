@@ -71,6 +71,9 @@ def make_c1():
     beta = np.loadtxt(os.path.join(out, "final.beta"))
     np.savetxt(os.path.join(out, "final.gamma.rows50"), gam[::50], fmt="%.10f")
     np.savetxt(os.path.join(out, "final.beta.cols25"), beta[:, ::25], fmt="%.10f")
+    # the whole of both files as the doubles their 10-decimal text parses to (for the chain-level
+    # ranked-list test: reference EM -> lda_post.py shaping -> scoring, beside the GPU chain)
+    np.savez_compressed(os.path.join(out, "final_full.npz"), gamma=gam, beta=beta)
     os.remove(os.path.join(out, "final.gamma"))
     os.remove(os.path.join(out, "final.beta"))
     with open(os.path.join(out, "corpus.txt"), "w") as f:
@@ -179,5 +182,7 @@ def main():
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "c2":
         make_c2(int(sys.argv[2]) if len(sys.argv) > 2 else None)
+    elif len(sys.argv) > 1 and sys.argv[1] == "c1":
+        make_c1()
     else:
         main()

@@ -72,6 +72,8 @@ def lib():
         L.orc_text_roundtrip.restype = C.c_double
         L.orc_theta_from_gamma.argtypes = [C.c_int, C.c_int, _f64p, _f64p]
         L.orc_pwz_from_beta.argtypes = [C.c_int, C.c_int, _f64p, _f64p]
+        L.orc_theta_from_gamma_raw.argtypes = [C.c_int, C.c_int, _f64p, _f64p]
+        L.orc_pwz_from_beta_raw.argtypes = [C.c_int, C.c_int, _f64p, _f64p]
         L.orc_score_flow.argtypes = [C.c_int64, C.c_int, _f64p, _f64p, _i32p, _i32p, _i32p,
                                      _i32p, _f64p, _f64p]
         L.orc_score_dns.argtypes = [C.c_int64, C.c_int, _f64p, _f64p, _i32p, _i32p, _f64p]

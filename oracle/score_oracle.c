@@ -72,6 +72,33 @@ void orc_pwz_from_beta(int K, int V, const double *beta, double *pwz)
     free(raw);
 }
 
+/* The same two shapings WITHOUT the 12-digit text round trip: the arithmetic of lda_post.py:45-50
+ * and :88-96 alone, which tests/golden/post pins (values produced by those source lines
+ * themselves under Python 3, oracle/pin_lda_post.py). */
+void orc_theta_from_gamma_raw(int D, int K, const double *gamma, double *theta)
+{
+    for (int d = 0; d < D; d++) {
+        const double *g = gamma + (size_t)d * K;
+        double total = 0;
+        for (int k = 0; k < K; k++) total = total + g[k];
+        for (int k = 0; k < K; k++) theta[(size_t)d * K + k] = (total > 0) ? g[k] / total : 0.0;
+    }
+}
+
+void orc_pwz_from_beta_raw(int K, int V, const double *beta, double *pwz)
+{
+    double *raw = malloc(sizeof(double) * (size_t)V);
+    for (int k = 0; k < K; k++) {
+        double total = 0;
+        for (int w = 0; w < V; w++) {
+            raw[w] = exp(beta[(size_t)k * V + w]);
+            total = total + raw[w];
+        }
+        for (int w = 0; w < V; w++) pwz[(size_t)w * K + k] = raw[w] / total;
+    }
+    free(raw);
+}
+
 static inline double dot_seq(const double *a, const double *b, int K)
 {
     volatile double acc = 0.0; /* volatile: forbid contraction/reassociation */

@@ -133,6 +133,21 @@ def test_lda_post_tables_match_oracle(golden_dir):
     assert np.allclose(theta.sum(1), 1.0, atol=1e-10)
 
 
+def test_lda_post_arithmetic_matches_the_reference_script(golden_dir):
+    """oni_lda_post with text_digits=0 against tests/golden/post: the values the reference's own
+    lda_post.py lines (:45-50, :88-96) produce under Python 3 (oracle/pin_lda_post.py)."""
+    import os
+    from oni_ml_b200 import files
+    g = os.path.join(golden_dir, "c0_k20")
+    gamma = files.read_matrix(os.path.join(g, "final.gamma"))
+    beta = files.read_matrix(os.path.join(g, "final.beta"))
+    want_theta = np.load(os.path.join(golden_dir, "post", "theta.npy"))
+    want_pwz = np.load(os.path.join(golden_dir, "post", "pwz.npy"))
+    theta, pwz = scoring.lda_post(gamma, beta, 0)
+    assert np.max(np.abs(theta - want_theta) / want_theta) < 1e-15
+    assert np.max(np.abs(pwz - want_pwz) / want_pwz) < 2e-12  # the device exp is a few ulp from numpy's
+
+
 def test_lda_post_files_csvs(golden_dir, tmp_path):
     """oni_lda_post_files: doc_results.csv / word_results.csv in lda_post.py's shapes, values
     equal to the oracle's 12-digit tables, names cut to 20 bytes, ".0" on integral values."""

@@ -91,3 +91,29 @@ def test_reference_binary_reproduces_golden(tmp_path, golden_dir):
                    check=True, env=env, stdout=subprocess.DEVNULL)
     for name in ("likelihood.dat", "final.gamma", "final.other"):
         assert _text(out / name) == _text(os.path.join(d, name))
+
+
+def test_post_shaping_arithmetic_pinned_to_the_reference_script(golden_dir):
+    """tests/golden/post holds theta and p(w|z) as the reference's OWN source lines compute them
+    (lda_post.py:45-50 and :88-96 executed under Python 3 by oracle/pin_lda_post.py, at full double
+    precision).  The C restatement must give the same values: theta exactly (one division per
+    entry), p(w|z) to the last bits (numpy's exp against glibc's).  The 12-digit text layer on top
+    of these values stays a restated convention (no Python 2 here)."""
+    from oni_ml_b200 import files
+    g = os.path.join(golden_dir, "c0_k20")
+    gamma = files.read_matrix(os.path.join(g, "final.gamma"))
+    beta = files.read_matrix(os.path.join(g, "final.beta"))
+    want_theta = np.load(os.path.join(golden_dir, "post", "theta.npy"))
+    want_pwz = np.load(os.path.join(golden_dir, "post", "pwz.npy"))
+    L = pyoracle.lib()
+    th = np.zeros_like(gamma); pw = np.zeros((beta.shape[1], beta.shape[0]))
+    L.orc_theta_from_gamma_raw(gamma.shape[0], gamma.shape[1], gamma, th)
+    L.orc_pwz_from_beta_raw(beta.shape[0], beta.shape[1], beta, pw)
+    assert np.array_equal(th, want_theta)
+    assert np.max(np.abs(pw - want_pwz) / want_pwz) < 1e-15
+    # and the 12-digit values the pipeline carries are these values rounded
+    th12 = np.zeros_like(gamma); pw12 = np.zeros_like(pw)
+    L.orc_theta_from_gamma(gamma.shape[0], gamma.shape[1], gamma, th12)
+    L.orc_pwz_from_beta(beta.shape[0], beta.shape[1], beta, pw12)
+    assert np.max(np.abs(th12 - want_theta) / want_theta) < 1e-11
+    assert np.max(np.abs(pw12 - want_pwz) / want_pwz) < 1e-11
