@@ -831,6 +831,10 @@ static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
     if (cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]) == cudaSuccess) c->stats.ms_suffstats = ms;
     if (cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]) == cudaSuccess) c->stats.ms_mstep = ms;
     c->stats.kernel_launches = c->launches;
+    if (nan_flag == 2) {  // (ONI_RING_CHECK builds only)
+        cudaMemsetAsync(c->d_nan, 0, sizeof(int32_t), c->stream);
+        return oni_set_error(ONI_ERR_CUDA, "ring self-check: a word visit of the long-document kernel read something else than plain loads of the same words");
+    }
     if (nan_flag || lik != lik) {
         cudaMemsetAsync(c->d_nan, 0, sizeof(int32_t), c->stream);  // reported once; the handle stays usable
         return oni_set_error(ONI_ERR_NAN, "a document bound is NaN (EM iteration %d)", c->em_iter + 1);

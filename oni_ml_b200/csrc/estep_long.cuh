@@ -168,6 +168,7 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
             unsigned pr_p = 0;
 #pragma unroll
             for (int t = 0; t < T; t++) e_p[t] = psi_p[t] = cl_p[t] = 0.0;
+#pragma unroll 4
             for (int i = 0; i < m; i++) {
                 // ---- one word visit (lda-inference.c:50-75); straight-line.  A lone warp issues
                 // in order, so the order below is the schedule: first what the chain needs next
@@ -228,6 +229,23 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
                 if (nd == len) { nd = 0; od = 0; wrapped = true; }
                 if (nt == len) nt = 0;
 
+#ifdef ONI_RING_CHECK
+                // Self-check build (profiles/ring_check.sh; compute-sanitizer is closed on this pool):
+                // what the ring delivered for THIS visit against plain loads of the same words --
+                // a copy that lands late, lands in the wrong slot or is overwritten early shows here.
+                {
+                    const int2 tk_direct = tok[pr_now / kp];
+                    bool okv = (c == (double)tk_direct.y);
+#pragma unroll
+                    for (int t = 0; t < T; t++) {
+                        if (!ok[t]) continue;
+                        okv = okv && (lb[t] == p.logbeta_t[(size_t)tk_direct.x * KP + lane + 32 * t]);
+                        const double want_old = (pass == 0) ? inv_k : phi[pr_now + lane + 32 * t];
+                        okv = okv && (old[t] == want_old);
+                    }
+                    if (!okv) atomicExch(p.nan_flag, 2);
+                }
+#endif
                 double cl[T], psi[T], e[T];
                 double sl = 0.0;
 #pragma unroll
@@ -356,11 +374,11 @@ __global__ void __launch_bounds__(NW * 32, 1) estep_long_kernel(const EstepParam
         // tables: psi | exk are contiguous in shared memory and come from two global arrays
         const double2 *a = reinterpret_cast<const double2 *>(p.psi_tab);
         double2 *d = reinterpret_cast<double2 *>(smem + L::psi);
-#pragma unroll 8
+#pragma unroll 4
         for (int i = threadIdx.x; i < PSI_N * PSI_COEF / 2; i += blockDim.x) d[i] = __ldg(a + i);
         const double2 *b = reinterpret_cast<const double2 *>(p.exk_tab);
         d = reinterpret_cast<double2 *>(smem + L::exk);
-#pragma unroll 8
+#pragma unroll 4
         for (int i = threadIdx.x; i < EXK_N / 2; i += blockDim.x) d[i] = __ldg(b + i);
         const double *src = reinterpret_cast<const double *>(&g_math_tables.lg[0]);
         double *dst = reinterpret_cast<double *>(smem + L::lg);
