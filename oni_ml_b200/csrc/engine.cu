@@ -483,6 +483,21 @@ static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_setti
         ONI_CUDA(cudaMemcpy(c->d_long_tabs, tabs.data(), sizeof(double) * tabs.size(), cudaMemcpyHostToDevice));
     }
     ONI_TRY(dev_alloc(&c->d_logbeta_t, (size_t)V * c->KP));
+    if (getenv("ONI_LDA_L2_PERSIST") && atoi(getenv("ONI_LDA_L2_PERSIST")) > 0) {
+        // Experiment (profiles/r2_estep_experiments.txt): keep the log-beta table (8 MB at flow-day
+        // size) in a persisting L2 window, so that the phi rows streaming through the L2 (267 GB per
+        // launch) do not evict the rows every word visit gathers.
+        const size_t bytes = sizeof(double) * (size_t)V * c->KP;
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min<size_t>(bytes, (size_t)prop.persistingL2CacheMaxSize));
+        cudaStreamAttrValue av{};
+        av.accessPolicyWindow.base_ptr = c->d_logbeta_t;
+        av.accessPolicyWindow.num_bytes = std::min<size_t>(bytes, (size_t)prop.accessPolicyMaxWindowSize);
+        av.accessPolicyWindow.hitRatio = 1.0f;
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        for (cudaStream_t st2 : {c->stream, c->stream_long, c->stream_excl})
+            ONI_CUDA(cudaStreamSetAttribute(st2, cudaStreamAttributeAccessPolicyWindow, &av));
+    }
     ONI_TRY(dev_alloc(&c->d_alpha, 1));
     ONI_TRY(dev_alloc(&c->d_ss, c->ss_count()));
     ONI_TRY(dev_alloc(&c->d_block_partial, (size_t)DOC_RED_BLOCKS * 3));

@@ -214,9 +214,29 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
         for (int i = threadIdx.x; i < (int)(sizeof(MathTables) / sizeof(double)); i += blockDim.x)
             dst[i] = src[i];
     }
+#ifdef ONI_ESTEP_REPL
+    // Experiment (profiles/r2_estep_experiments.txt): bank-interleaved copies of the two tables in
+    // dynamic shared memory.  A table read is one lane = one random entry; the 16 lanes of a
+    // half-warp (LDS.64) or the 8 lanes of a quarter-warp (LDS.128) then collide in banks ~3-deep.
+    // With copy r = lane mod 16 (mod 8) laid out entry-major, every lane of a phase owns a bank.
+    extern __shared__ __align__(16) unsigned char repl_smem[];
+    double *const ex_rep = reinterpret_cast<double *>(repl_smem);                                  // [256][16]
+    LogEntry *const lg_rep = reinterpret_cast<LogEntry *>(repl_smem + sizeof(double) * ONI_MT_N * 16);  // [256][8]
+    for (int i = threadIdx.x; i < ONI_MT_N * 16; i += blockDim.x) ex_rep[i] = g_math_tables.ex[i >> 4];
+    for (int i = threadIdx.x; i < ONI_MT_N * 8; i += blockDim.x) lg_rep[i] = g_math_tables.lg[i >> 3];
+#endif
     __syncthreads();
 
     const int lane = threadIdx.x & 31;
+#ifdef ONI_ESTEP_REPL
+    constexpr int XS = 16, LS = 8;
+    const double *const ex_l = ex_rep + (lane & 15);
+    const LogEntry *const lg_l = lg_rep + (lane & 7);
+#else
+    constexpr int XS = 1, LS = 1;
+    const double *const ex_l = tabs.ex;
+    const LogEntry *const lg_l = tabs.lg;
+#endif
     const int j = lane & (G - 1);
     const int lead = lane & ~(G - 1);
     const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << lead);
@@ -263,7 +283,7 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
                 s_keep = 1.0; c_keep = 0.0;
                 // lda-inference.c:37-43
                 const double g0 = alpha + p.doc_total[doc] / ((double)K);
-                const double d0 = digamma_ref(g0, tabs.lg);
+                const double d0 = digamma_ref<LS>(g0, lg_l);
 #pragma unroll
                 for (int t = 0; t < T; t++) {
                     const bool ok = (t < T - 1) || last_ok;
@@ -387,7 +407,7 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             double s = 0.0;
 #pragma unroll
             for (int t = 0; t < T; t++) {
-                const double e = exp_tab(SHIFT ? (x[t] - shift) : x[t], tabs.ex);
+                const double e = exp_tab<XS>(SHIFT ? (x[t] - shift) : x[t], ex_l);
                 x[t] = ((t < T - 1) || last_ok) ? e : 0.0;
                 s += x[t];
             }
@@ -428,7 +448,7 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             }
 #pragma unroll
             for (int t = 0; t < T; t++)
-                dg[t] = LAT ? digamma_ref_lat(gam[t], tabs.lg) : digamma_ref(gam[t], tabs.lg);
+                dg[t] = LAT ? digamma_ref_lat(gam[t], tabs.lg) : digamma_ref<LS>(gam[t], lg_l);
 #pragma unroll
             for (int t = 0; t < T; t++)
                 if ((t < T - 1) || last_ok) phrow[j + G * t] = x[t];
@@ -459,7 +479,7 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             if (slot == j) { s_keep = s; c_keep = c; }
             pos++;
             if (slot == G - 1 || pos == end) {
-                acc_b = fma(c_keep, log_tab(s_keep, tabs.lg), acc_b);
+                acc_b = fma(c_keep, log_tab<LS>(s_keep, lg_l), acc_b);
                 s_keep = 1.0; c_keep = 0.0;
             }
         }
@@ -475,7 +495,7 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             for (int t = 0; t < T; t++) {
                 const bool ok = (t < T - 1) || last_ok;
                 gs += ok ? gam[t] : 0.0;
-                part += ok ? lgamma_pos(gam[t], tabs.lg) : 0.0;
+                part += ok ? lgamma_pos<LS>(gam[t], lg_l) : 0.0;
             }
             part += acc_b - acc_a;
 #pragma unroll
@@ -483,7 +503,7 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
                 gs += __shfl_xor_sync(gmask, gs, o);
                 part += __shfl_xor_sync(gmask, part, o);
             }
-            const double lik = (lik_const - lgamma_pos(gs, tabs.lg)) + part + (SHIFT ? acc_s : 0.0);
+            const double lik = (lik_const - lgamma_pos<LS>(gs, lg_l)) + part + (SHIFT ? acc_s : 0.0);
             pass++;
             // lda-inference.c:79-80 and the loop condition :46-47
             const double conv = (lik_old - lik) / lik_old;
@@ -511,7 +531,7 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
                 ds = group_sum<G>(ds, gmask);
                 if (j == 0) {
                     p.doc_lik[doc] = lik;
-                    p.doc_ass[doc] = ds - K * digamma_ref(gs, tabs.lg);
+                    p.doc_ass[doc] = ds - K * digamma_ref<LS>(gs, lg_l);
                     p.doc_iters[doc] = pass;
                 }
                 have = false;
