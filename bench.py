@@ -138,7 +138,8 @@ class ClockSampler:
 
 # ------------------------------------------------------------------ reference arm
 def make_sample_model_dat(path, docs, seed=20160123):
-    from oni_ml_b200.corpus import synth_corpus, write_model_dat
+    from harness.synth import synth_corpus
+    from oni_ml_b200.corpus import write_model_dat
     c = synth_corpus(docs, WORKLOAD["vocab"], k_true=K_TOPICS, mu=WORKLOAD["mu"],
                      geom_p=WORKLOAD["geom_p"], seed=seed)
     write_model_dat(path, c)
@@ -288,7 +289,7 @@ def _em_corpus(args, shape, scaling, rank, world, dev):
     its ranks, lda-estimate.c:201.  weak: every rank draws its own documents over shared topics."""
     import torch
     from oni_ml_b200 import dist as odist
-    from oni_ml_b200.corpus import synth_corpus
+    from harness.synth import synth_corpus
     V = WORKLOAD["vocab"]
     kw = dict(k_true=K_TOPICS, mu=WORKLOAD["mu"], geom_p=WORKLOAD["geom_p"], dup_frac=shape.get("dup_frac", 0.02),
               device=dev, as_torch=True)
@@ -314,6 +315,7 @@ def _em_measure(args, shape, scaling, rank, world, local, dev, with_e2e):
     the global figures)."""
     import torch
     import torch.distributed as dist
+    from harness.torchrun import bootstrap_nccl
     from oni_ml_b200 import _lib, dist as odist, lda
     from oni_ml_b200.corpus import Corpus
 
@@ -328,7 +330,7 @@ def _em_measure(args, shape, scaling, rank, world, local, dev, with_e2e):
     eng.set_corpus_device(ptr, word, count)
     eng.init_random(SEED, ALPHA)
     if world > 1:
-        odist.bootstrap_nccl(eng, rank, world)
+        bootstrap_nccl(eng, rank, world)
     stream = torch.cuda.ExternalStream(eng.stream_ptr(), device=dev)
 
     def sync_all():
@@ -450,6 +452,7 @@ def multi_gpu_parity(rank, world, local, dev):
     reference's own files.  Returns the largest relative error over all ranks."""
     import torch
     import torch.distributed as dist
+    from harness.torchrun import bootstrap_nccl
     from oni_ml_b200 import _lib, dist as odist, files, lda
     g = os.path.join(ROOT, "tests", "golden")
     c = lda.read_corpus(os.path.join(g, "c0_model.dat"))
@@ -461,7 +464,7 @@ def multi_gpu_parity(rank, world, local, dev):
     with lda.LdaEngine(local, 20, c.num_terms, st) as eng:
         eng.set_corpus(mine)
         eng.init_random(4357, 2.5)
-        odist.bootstrap_nccl(eng, rank, world)
+        bootstrap_nccl(eng, rank, world)
         lik, _ = odist.run_em(eng)
         gam = eng.gamma()
     err = 1.0

@@ -4,9 +4,10 @@ The reference shards documents round-robin over MPI ranks and reduces the
 sufficient statistics with 2K+3 MPI_Allreduce calls per EM iteration
 (oni-lda-c/lda-estimate.c:201,211-252).  Here every rank (= one process = one
 GPU) owns a contiguous, pair-balanced block of documents and the packed
-statistics are summed by ONE all-reduce per iteration.  torch.distributed is
-only the bootstrap (rank discovery, broadcast of the NCCL id); the data-path
-collective is the library's ncclAllReduce on the engine's own stream.
+statistics are summed by ONE all-reduce per iteration: the library's
+ncclAllReduce on the engine's own stream.  How the 128-byte NCCL id reaches the
+ranks is the launcher's business (harness/torchrun.py does it with
+torch.distributed for the tests and bench.py).
 """
 from __future__ import annotations
 
@@ -27,16 +28,6 @@ def shard_bounds(doc_ptr: np.ndarray, nranks: int) -> list[int]:
         pos = int(np.searchsorted(doc_ptr, target, side="left"))
         cut[r] = max(cut[r - 1], min(pos, d))
     return cut
-
-
-def bootstrap_nccl(engine, rank: int, world: int) -> None:
-    """Rank 0 makes the NCCL id, torch.distributed carries the 128 bytes, every
-    rank joins the library's communicator."""
-    import torch.distributed as dist
-    from . import lda
-    box = [lda.nccl_unique_id() if rank == 0 else None]
-    dist.broadcast_object_list(box, src=0)
-    engine.comm_init(box[0], rank, world)
 
 
 def em_iteration(engine, allreduce: Callable[[], None] | None = None):

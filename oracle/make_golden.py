@@ -24,7 +24,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from oni_ml_b200.corpus import Corpus, synth_corpus, write_model_dat  # noqa: E402
+from harness.synth import synth_corpus
+from oni_ml_b200.corpus import Corpus, write_model_dat  # noqa: E402
 
 REF = os.path.join(ROOT, "oracle", "_ref", "lda_ref")
 GOLD = os.path.join(ROOT, "tests", "golden")

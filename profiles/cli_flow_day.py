@@ -1,7 +1,7 @@
 import sys, time, os, numpy as np, subprocess
 sys.path.insert(0, os.getcwd())
 import torch
-from oni_ml_b200.corpus import synth_corpus
+from harness.synth import synth_corpus
 from oni_ml_b200 import LDA_BIN
 ptr, word, count = synth_corpus(1_000_000, 50_000, mu=3.5, seed=20160123, device="cuda", as_torch=True)
 ptr, word, count = ptr.cpu().numpy(), word.cpu().numpy(), count.cpu().numpy()

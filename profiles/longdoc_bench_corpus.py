@@ -4,7 +4,7 @@ sys.path.insert(0, os.getcwd())
 os.environ["ONI_LDA_TIMING"] = "1"
 import torch
 from oni_ml_b200 import _lib, lda
-from oni_ml_b200.corpus import synth_corpus
+from harness.synth import synth_corpus
 V, K = 50000, 20
 ptr, word, count = synth_corpus(1_000_000, V, k_true=20, mu=3.5, geom_p=0.25, seed=20160123, device="cuda", as_torch=True, topic_seed=20160123)
 lens = (ptr[1:] - ptr[:-1]).cpu().numpy()

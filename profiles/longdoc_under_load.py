@@ -6,7 +6,8 @@ sys.path.insert(0, os.getcwd())
 os.environ["ONI_LDA_TIMING"] = "1"
 import torch
 from oni_ml_b200 import _lib, lda
-from oni_ml_b200.corpus import Corpus, synth_corpus
+from harness.synth import synth_corpus
+from oni_ml_b200.corpus import Corpus
 
 V, K, N = 50000, 20, 8000
 bg = synth_corpus(int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000, V, mu=3.5, seed=20160123)  # max doc 3657

@@ -5,7 +5,8 @@ import os, sys
 import numpy as np
 sys.path.insert(0, os.getcwd())
 from oni_ml_b200 import _lib, lda
-from oni_ml_b200.corpus import Corpus, synth_corpus
+from harness.synth import synth_corpus
+from oni_ml_b200.corpus import Corpus
 
 V, K, N = 50000, 20, int(sys.argv[2]) if len(sys.argv) > 2 else 8000
 bg = synth_corpus(int(sys.argv[1]) if len(sys.argv) > 1 else 125_000, V, mu=3.5, seed=20160123)

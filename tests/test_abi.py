@@ -171,3 +171,30 @@ def test_product_never_touches_the_oracle():
     import subprocess
     deps = subprocess.run(["ldd", _lib.LIB_PATH], capture_output=True, text=True).stdout
     assert "oracle" not in deps and "torch" not in deps
+
+
+def test_product_package_needs_no_torch():
+    """north_star: "no PyTorch".  The Python side of the product is a ctypes binding; importing every
+    module of oni_ml_b200 must not pull torch in (the corpus generator and the torchrun bootstrap,
+    which do use it, live under harness/)."""
+    import subprocess
+    import sys
+    code = ("import sys, oni_ml_b200, oni_ml_b200._lib, oni_ml_b200.lda, oni_ml_b200.scoring, oni_ml_b200.files, "
+            "oni_ml_b200.corpus, oni_ml_b200.dist, oni_ml_b200.events; oni_ml_b200._lib.load(); "
+            "print('torch' in sys.modules)")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=ROOT)
+    assert out.returncode == 0, out.stderr
+    assert out.stdout.strip() == "False"
+
+
+def test_write_corpus_is_the_inverse_of_read_corpus(tmp_path, c0_corpus, golden_dir):
+    """oni_lda_write_corpus writes the model.dat text lda_pre.py:94 writes (the committed fixture
+    byte for byte) and what it writes parses back to the same arrays."""
+    p = str(tmp_path / "model.dat")
+    lda.write_corpus(p, c0_corpus)
+    assert open(p).read() == open(os.path.join(golden_dir, "c0_model.dat")).read()
+    back = lda.read_corpus(p)
+    assert np.array_equal(back.doc_ptr, c0_corpus.doc_ptr) and np.array_equal(back.word, c0_corpus.word)
+    assert np.array_equal(back.count, c0_corpus.count)
+    with pytest.raises(_lib.OniError):
+        lda.write_corpus(str(tmp_path / "no" / "dir" / "model.dat"), c0_corpus)

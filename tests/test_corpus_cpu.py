@@ -4,7 +4,8 @@ import os
 
 import numpy as np
 
-from oni_ml_b200.corpus import Corpus, read_model_dat, synth_corpus, write_model_dat
+from harness.synth import synth_corpus
+from oni_ml_b200.corpus import Corpus, read_model_dat, write_model_dat
 
 
 def _word_mass(c):

@@ -26,7 +26,7 @@ import numpy as np
 import pytest
 
 from oni_ml_b200 import files, lda, scoring
-from oni_ml_b200.corpus import synth_corpus
+from harness.synth import synth_corpus
 from oracle import pyoracle
 
 pytestmark = pytest.mark.gpu

@@ -14,7 +14,8 @@ import numpy as np
 import pytest
 
 from oni_ml_b200 import _lib, files, lda
-from oni_ml_b200.corpus import Corpus, synth_corpus
+from harness.synth import synth_corpus
+from oni_ml_b200.corpus import Corpus
 from oracle import pyoracle
 
 pytestmark = pytest.mark.gpu
