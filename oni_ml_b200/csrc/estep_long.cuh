@@ -158,6 +158,15 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
         old[t] = sh.old[t * 32];
     }
     double2 *const keep = reinterpret_cast<double2 *>(sh.keep);
+    // the psi-table coefficients of the interval each topic's gamma is in (none yet)
+    double2 c01[T], c23[T], c45[T];
+    unsigned held[T];
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+        held[t] = 0xffffffffu;
+        c01[t] = c23[t] = c45[t] = make_double2(0.0, 0.0);
+    }
+    const unsigned psi_saddr = (unsigned)__cvta_generic_to_shared(sh.psi);
 
     for (;;) {  // sweeps
         unsigned pr = 0;  // phi offset of the row of this visit
@@ -174,7 +183,6 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
                 // in order, so the order below is the schedule: first what the chain needs next
                 // (the table rows of the new gamma), then, while those are on their way, the
                 // leftovers of the previous visit and the requests for later ones.
-                double2 c01[T], c23[T], c45[T];
                 double r[T];
 #pragma unroll
                 for (int t = 0; t < T; t++) {
@@ -182,8 +190,19 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
                         const unsigned idx_raw = (unsigned)psi_index(gam[t]);
                         bad = max(bad, idx_raw);  // (negative indices are huge as unsigned)
                         const unsigned idx = min(idx_raw, (unsigned)(PSI_N - 1));
-                        const double2 *cf = reinterpret_cast<const double2 *>(sh.psi + idx * PSI_COEF);
-                        c01[t] = cf[0]; c23[t] = cf[1]; c45[t] = cf[2];
+                        // The six coefficients stay in registers from visit to visit and are read again
+                        // only when gamma has moved to another interval (1.6 % wide: after the first
+                        // sweep or two a rare event), by loads predicated per lane -- no branch, and the
+                        // polynomial below does not wait for shared memory when nothing was read.
+                        const unsigned addr = psi_saddr + idx * (unsigned)(PSI_COEF * sizeof(double));
+                        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %6, %7;\n\t"
+                                     "@p ld.shared.v2.f64 {%0, %1}, [%8];\n\t"
+                                     "@p ld.shared.v2.f64 {%2, %3}, [%8+16];\n\t"
+                                     "@p ld.shared.v2.f64 {%4, %5}, [%8+32];\n\t}"
+                                     : "+d"(c01[t].x), "+d"(c01[t].y), "+d"(c23[t].x), "+d"(c23[t].y), "+d"(c45[t].x),
+                                       "+d"(c45[t].y)
+                                     : "r"(idx), "r"(held[t]), "r"(addr));
+                        held[t] = idx;
                         r[t] = gam[t] - psi_centre(gam[t]);
                     }
                 }
