@@ -268,7 +268,11 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
                 double lb_n[T], old_n[T];
 #pragma unroll
                 for (int t = 0; t < T; t++) {
+#ifdef ONI_RING_CHECK_BREAK
+                    lb_n[t] = sh.lb[(((v + 2) & (QD - 1)) * T + t) * 32];  // negative control of the self-check: the wrong slot
+#else
                     lb_n[t] = sh.lb[(((v + 1) & (QD - 1)) * T + t) * 32];
+#endif
                     old_n[t] = sh.old[(((v + 1) & (QD - 1)) * T + t) * 32];
                 }
 

@@ -13,3 +13,8 @@ echo "== long-document tests on the self-check build ($ONI_LDA_LIB)"
 python -m pytest tests/test_gpu_lda.py -q -m gpu -k "long_document or leaves_the or flow_day_size or config1_full"
 echo "== a single 8000-pair document, 3 EM iterations"
 python profiles/longdoc_single.py
+
+echo "== negative control: the same build with the next visit's row read from the wrong ring slot (-DONI_RING_CHECK_BREAK) must FAIL the check"
+make -C oni_ml_b200/csrc -j BUILD=build_check2 OUTLIB=../variants/liboni_lda_check2.so OUTBIN=../variants/lda_check2 \
+     EXTRA="-DONI_RING_CHECK -DONI_RING_CHECK_BREAK" > /dev/null
+ONI_LDA_LIB=$PWD/oni_ml_b200/variants/liboni_lda_check2.so python profiles/longdoc_single.py 2>&1 | tail -2 || true
