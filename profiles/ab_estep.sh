@@ -1,3 +1,5 @@
+# A/B runs of the main E-step launch on ONE box: bench.py with the default build and with variant builds
+# (ONI_LDA_LIB) or runtime knobs.  usage: bash profiles/ab_estep.sh name=ENV=VALUE[,ENV=VALUE] ...
 run() { # name, env...
   name=$1; shift
   env "$@" python bench.py --steps 8 --warmup 3 --no-cpu-baseline --no-cli --no-scoring > gpurun_out/ab_$name.json 2>/dev/null
@@ -7,7 +9,8 @@ print("%-18s step %.2f ms  E-step %.2f ms  clocks %s" % ("$name", d["ms_per_step
 PY
 }
 run base A=1
-run l2persist ONI_LDA_L2_PERSIST=1
-run repl ONI_LDA_LIB=$PWD/oni_ml_b200/variants/liboni_lda_repl.so
-run repl_l2 ONI_LDA_LIB=$PWD/oni_ml_b200/variants/liboni_lda_repl.so ONI_LDA_L2_PERSIST=1
+for spec in "$@"; do
+  name=${spec%%=*}; envs=${spec#*=}
+  run $name $(echo $envs | tr ',' ' ')
+done
 run base2 A=1
