@@ -110,9 +110,12 @@ struct oni_lda_ctx {
                 ev_t_long = nullptr, ev_t_excl = nullptr, ev_t_main = nullptr;  // ONI_LDA_TIMING: ends of the three launches
     int sm_count = 0;
 
-    // corpus shard
+    // corpus shard.  The buffers grow and never shrink while the context lives: a caller that
+    // runs job after job on one handle (bench.py's e2e, a daily pipeline) pays cudaMalloc / cudaFree
+    // of ~10 GB once -- those calls were seen to take anything between 30 and 300 ms.
     int D = 0;
     int64_t nnz = 0;
+    size_t cap_docs = 0, cap_pairs = 0, cap_items = 0, cap_items2 = 0, cap_partial = 0;
     int2 *d_tok = nullptr;
     int64_t *d_doc_ptr = nullptr;
     int32_t *d_order = nullptr;
@@ -178,16 +181,24 @@ int dev_alloc(Tp **p, size_t n)
     return ONI_OK;
 }
 
-void free_corpus(oni_lda_ctx *c)
+// the buffers sized by the number of documents / pairs
+void free_corpus_buffers(oni_lda_ctx *c)
 {
     cudaFree(c->d_tok); cudaFree(c->d_doc_ptr); cudaFree(c->d_order); cudaFree(c->d_doc_total);
-    cudaFree(c->d_perm); cudaFree(c->d_items); cudaFree(c->d_items2); cudaFree(c->d_phi);
+    cudaFree(c->d_perm); cudaFree(c->d_phi);
     cudaFree(c->d_gamma); cudaFree(c->d_doc_lik); cudaFree(c->d_doc_ass); cudaFree(c->d_doc_iters);
-    cudaFree(c->d_partial);
     c->d_tok = nullptr; c->d_doc_ptr = nullptr; c->d_order = nullptr; c->d_doc_total = nullptr;
-    c->d_perm = nullptr; c->d_items = c->d_items2 = nullptr; c->d_phi = nullptr;
+    c->d_perm = nullptr; c->d_phi = nullptr;
     c->d_gamma = c->d_doc_lik = c->d_doc_ass = nullptr; c->d_doc_iters = nullptr;
-    c->d_partial = nullptr;
+    c->cap_docs = c->cap_pairs = 0;
+}
+
+void free_corpus(oni_lda_ctx *c)
+{
+    free_corpus_buffers(c);
+    cudaFree(c->d_items); cudaFree(c->d_items2); cudaFree(c->d_partial);
+    c->d_items = c->d_items2 = nullptr; c->d_partial = nullptr;
+    c->cap_items = c->cap_items2 = c->cap_partial = 0;
     c->D = 0; c->nnz = 0; c->n_long = 0; c->n_excl = 0;
 }
 
@@ -253,33 +264,46 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     }
     tm.lap("validate doc_ptr");
 
-    free_corpus(c);
     c->D = D; c->nnz = nnz; c->n_long = n_long; c->n_excl = n_excl; c->max_doc_pairs = max_pairs;
     cudaStream_t s = c->stream;
-    ONI_TRY(dev_alloc(&c->d_tok, (size_t)nnz));
-    ONI_TRY(dev_alloc(&c->d_doc_ptr, (size_t)D + 1));
-    ONI_TRY(dev_alloc(&c->d_order, (size_t)D));
-    ONI_TRY(dev_alloc(&c->d_doc_total, (size_t)D));
-    ONI_TRY(dev_alloc(&c->d_perm, (size_t)nnz));
-    ONI_TRY(dev_alloc(&c->d_phi, (size_t)nnz * c->KP));
-    ONI_TRY(dev_alloc(&c->d_gamma, (size_t)D * c->K));
-    ONI_TRY(dev_alloc(&c->d_doc_lik, (size_t)D));
-    ONI_TRY(dev_alloc(&c->d_doc_ass, (size_t)D));
-    ONI_TRY(dev_alloc(&c->d_doc_iters, (size_t)D));
-    // scratch of the two sorts (freed below)
+    if (!c->d_doc_ptr || (size_t)D > c->cap_docs || (size_t)nnz > c->cap_pairs) {
+        // (one of the two grew: everything sized by it is replaced; sizes are kept with a little headroom)
+        const size_t nd = std::max<size_t>((size_t)D, c->cap_docs), np = std::max<size_t>((size_t)nnz, c->cap_pairs);
+        ONI_CUDA(cudaStreamSynchronize(s));
+        free_corpus_buffers(c);
+        ONI_TRY(dev_alloc(&c->d_tok, np));
+        ONI_TRY(dev_alloc(&c->d_doc_ptr, nd + 1));
+        ONI_TRY(dev_alloc(&c->d_order, nd));
+        ONI_TRY(dev_alloc(&c->d_doc_total, nd));
+        ONI_TRY(dev_alloc(&c->d_perm, np));
+        ONI_TRY(dev_alloc(&c->d_phi, np * c->KP));
+        ONI_TRY(dev_alloc(&c->d_gamma, nd * c->K));
+        ONI_TRY(dev_alloc(&c->d_doc_lik, nd));
+        ONI_TRY(dev_alloc(&c->d_doc_ass, nd));
+        ONI_TRY(dev_alloc(&c->d_doc_iters, nd));
+        c->cap_docs = nd; c->cap_pairs = np;
+    }
+    // scratch of the two sorts: 4 x 8 bytes per entry, carved out of the phi buffer (unused until the
+    // first E-step) when it is large enough, i.e. whenever KP >= 4 pairs' worth covers the documents
     const size_t m = (size_t)std::max<int64_t>(nnz, D);
     const size_t ntiles = (m + RS_TILE - 1) / RS_TILE;
     unsigned long long *key[2] = {nullptr, nullptr}, *idx[2] = {nullptr, nullptr}, *counts = nullptr, *totals = nullptr;
     int64_t *d_wptr = nullptr;
+    const bool in_phi = 4 * m <= c->cap_pairs * (size_t)c->KP;
     int rc = ONI_OK;
     auto release = [&]() {
-        cudaFree(key[0]); cudaFree(key[1]); cudaFree(idx[0]); cudaFree(idx[1]);
+        if (!in_phi) { cudaFree(key[0]); cudaFree(key[1]); cudaFree(idx[0]); cudaFree(idx[1]); }
         cudaFree(counts); cudaFree(totals); cudaFree(d_wptr);
     };
 #define ONI_IDX(call) do { rc = (call); if (rc != ONI_OK) { release(); return rc; } } while (0)
 #define ONI_IDX_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { release(); \
         return oni_set_error(ONI_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } } while (0)
-    for (int b = 0; b < 2; b++) { ONI_IDX(dev_alloc(&key[b], m)); ONI_IDX(dev_alloc(&idx[b], m)); }
+    if (in_phi) {
+        unsigned long long *base = reinterpret_cast<unsigned long long *>(c->d_phi);
+        key[0] = base; key[1] = base + m; idx[0] = base + 2 * m; idx[1] = base + 3 * m;
+    } else {
+        for (int b = 0; b < 2; b++) { ONI_IDX(dev_alloc(&key[b], m)); ONI_IDX(dev_alloc(&idx[b], m)); }
+    }
     ONI_IDX(dev_alloc(&counts, 256 * ntiles));
     ONI_IDX(dev_alloc(&totals, (size_t)RS_MAX_PASSES * 256));
     ONI_IDX(dev_alloc(&d_wptr, (size_t)V + 1));
@@ -360,9 +384,12 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     }
     c->level_off = level_off;
     c->n_items = (int32_t)items.size(); c->n_items2 = (int32_t)items2.size(); c->n_partial = n_partial;
-    ONI_TRY(dev_alloc(&c->d_items, items.size()));
-    ONI_TRY(dev_alloc(&c->d_items2, items2.size()));
-    ONI_TRY(dev_alloc(&c->d_partial, (size_t)n_partial * c->KP));
+    if (items.size() > c->cap_items) { cudaFree(c->d_items); c->d_items = nullptr; c->cap_items = 0;
+        ONI_TRY(dev_alloc(&c->d_items, items.size())); c->cap_items = items.size(); }
+    if (items2.size() > c->cap_items2 || !c->d_items2) { cudaFree(c->d_items2); c->d_items2 = nullptr; c->cap_items2 = 0;
+        ONI_TRY(dev_alloc(&c->d_items2, items2.size())); c->cap_items2 = items2.size(); }
+    if ((size_t)n_partial > c->cap_partial || !c->d_partial) { cudaFree(c->d_partial); c->d_partial = nullptr; c->cap_partial = 0;
+        ONI_TRY(dev_alloc(&c->d_partial, (size_t)n_partial * c->KP)); c->cap_partial = (size_t)n_partial; }
     ONI_CUDA(cudaMemcpyAsync(c->d_items, items.data(), sizeof(SsItem) * items.size(), cudaMemcpyHostToDevice, s));
     ONI_CUDA(cudaMemcpyAsync(c->d_items2, items2.data(), sizeof(SsItem) * items2.size(), cudaMemcpyHostToDevice, s));
     ONI_CUDA(cudaStreamSynchronize(s));  // host vectors die at return
