@@ -5,17 +5,12 @@ from harness.synth import synth_corpus
 from oni_ml_b200 import LDA_BIN
 ptr, word, count = synth_corpus(1_000_000, 50_000, mu=3.5, seed=20160123, device="cuda", as_torch=True)
 ptr, word, count = ptr.cpu().numpy(), word.cpu().numpy(), count.cpu().numpy()
+from oni_ml_b200 import lda
+from oni_ml_b200.corpus import Corpus
 t = time.time()
 os.makedirs("/tmp/day", exist_ok=True)
-pairs = np.char.add(np.char.add(word.astype(str), ":"), count.astype(str))
-with open("/tmp/day/model.dat", "w") as f:
-    for d0 in range(0, 1_000_000, 20000):
-        out = []
-        for d in range(d0, min(d0 + 20000, 1_000_000)):
-            a, b = ptr[d], ptr[d + 1]
-            out.append(str(b - a) + " " + " ".join(pairs[a:b]))
-        f.write("\n".join(out) + "\n")
-print("model.dat: %.0f MB written in %.0f s" % (os.path.getsize("/tmp/day/model.dat") / 1e6, time.time() - t), flush=True)
+lda.write_corpus("/tmp/day/model.dat", Corpus(ptr, word, count, 50_000))
+print("model.dat: %.0f MB written in %.1f s" % (os.path.getsize("/tmp/day/model.dat") / 1e6, time.time() - t), flush=True)
 open("/tmp/day/settings.txt", "w").write("var max iter 20\nvar convergence 1e-6\nem max iter 20\nem convergence 1e-6\nalpha estimate\n")
 t = time.time()
 p = subprocess.run([LDA_BIN, "est", "2.5", "20", "/tmp/day/settings.txt", "1", "/tmp/day/model.dat", "random", "/tmp/day/out"],

@@ -55,6 +55,40 @@ def test_flow_ranked_list_identical(n, D, V, K, q):
     assert np.all(np.diff(got["key"]) >= 0)
 
 
+@pytest.mark.parametrize("chunk", [977, 4096, 65536])
+def test_chunked_upload_gives_the_same_list_and_sides(monkeypatch, chunk):
+    """Events from host arrays travel in chunks on a copy stream while the previous chunk is scored
+    (ONI_SCORE_CHUNK; 2^24 by default).  Any chunk size, also one that does not divide the event
+    count, must give the oracle's list -- indices, keys and the two per-side scores of the ranked
+    survivors (which are gathered on the host across chunks)."""
+    monkeypatch.setenv("ONI_SCORE_CHUNK", str(chunk))
+    n, D, V, K = 30011, 700, 500, 20
+    theta, pwz = tables(D, V, K, 5)
+    sd, dd, sw, dw = events(n, D, V, 6)
+    a, b, _, _ = oracle_flow(theta, pwz, sd, dd, sw, dw, np.inf)
+    tol = float(np.quantile(np.minimum(a, b), 0.05))
+    _, _, want_idx, want_key = oracle_flow(theta, pwz, sd, dd, sw, dw, tol)
+    got = scoring.score_flow(theta, pwz, sd, dd, sw, dw, tol)
+    assert got["n"] == want_idx.shape[0] and np.array_equal(got["idx"], want_idx)
+    assert np.array_equal(got["key"].view(np.int64), want_key.view(np.int64))
+    assert np.array_equal(got["src"].view(np.int64), a[want_idx].view(np.int64))
+    assert np.array_equal(got["dst"].view(np.int64), b[want_idx].view(np.int64))
+    # the context entry point a repeat caller uses: same events twice on one context, second run from a clean list
+    ctx = scoring.ScoreContext(theta, pwz, 0)
+    for _ in range(2):
+        ctx.begin(); ctx.score_flow_host(sd, dd, sw, dw, tol); m = ctx.rank()
+        idx, key = ctx.fetch(m)
+        assert m == want_idx.shape[0] and np.array_equal(idx, want_idx)
+        assert np.array_equal(key.view(np.int64), want_key.view(np.int64))
+    ctx.close()
+    # an index beyond its table, in the LAST chunk: refused by the kernel's own check
+    bad = sd.copy(); bad[-3] = D
+    from oni_ml_b200 import _lib
+    with pytest.raises(_lib.OniError) as e:
+        scoring.score_flow(theta, pwz, bad, dd, sw, dw, tol)
+    assert e.value.code == 1
+
+
 def test_ties_rank_by_event_index_and_misses_use_default_vector():
     K = 20
     theta = np.full((3, K), 0.05); pwz = np.full((4, K), 0.05)
