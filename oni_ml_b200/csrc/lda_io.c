@@ -18,6 +18,9 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <sys/types.h>
 #include <unistd.h>
 
 #include "../../include/oni_lda.h"
@@ -64,20 +67,52 @@ int oni_lda_read_settings(const char *path, oni_lda_settings *out)
 /* ------------------------------------------------------------------ corpus */
 /* Whole-file read + hand-rolled integer scan: the grammar is "N" followed by N
  * "w:c" tokens, whitespace (blank or newline) separated, lda-data.c:35-51. */
+typedef struct { int fd; char *dst; size_t off, n; int ok; } slurp_job;
+
+static void *slurp_slice(void *arg)
+{
+    slurp_job *j = arg;
+    size_t done = 0;
+    j->ok = 1;
+    while (done < j->n) {
+        ssize_t r = pread(j->fd, j->dst + done, j->n - done, (off_t)(j->off + done));
+        if (r <= 0) { j->ok = 0; break; }
+        done += (size_t)r;
+    }
+    return NULL;
+}
+
+/* The whole file in one NUL-terminated buffer; a large file is read by a few threads, one slice
+ * each (a 432 MB model.dat out of the page cache: 0.25 s with one fread, ~0.05 s this way). */
 static char *slurp(const char *path, size_t *len)
 {
-    FILE *f = fopen(path, "rb");
-    if (!f) return NULL;
-    if (fseek(f, 0, SEEK_END) != 0) { fclose(f); return NULL; }
-    long n = ftell(f);
-    if (n < 0) { fclose(f); return NULL; }
-    rewind(f);
-    char *buf = malloc((size_t)n + 1);
-    if (!buf) { fclose(f); errno = ENOMEM; return NULL; }
-    size_t got = fread(buf, 1, (size_t)n, f);
-    fclose(f);
-    buf[got] = 0;
-    *len = got;
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) return NULL;
+    struct stat st;
+    if (fstat(fd, &st) != 0 || st.st_size < 0) { close(fd); return NULL; }
+    const size_t n = (size_t)st.st_size;
+    char *buf = malloc(n + 1);
+    if (!buf) { close(fd); errno = ENOMEM; return NULL; }
+    enum { MAXT = 16 };
+    long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+    int nt = (int)(ncpu < 1 ? 1 : (ncpu > MAXT ? MAXT : ncpu));
+    if (n < ((size_t)8 << 20)) nt = 1;
+    slurp_job job[MAXT];
+    pthread_t th[MAXT];
+    int ok = 1;
+    for (int t = 0; t < nt; t++) {
+        const size_t a = n / (size_t)nt * (size_t)t, b = (t == nt - 1) ? n : n / (size_t)nt * (size_t)(t + 1);
+        job[t].fd = fd; job[t].dst = buf + a; job[t].off = a; job[t].n = b - a;
+        if (nt == 1 || pthread_create(&th[t], NULL, slurp_slice, &job[t]) != 0) { slurp_slice(&job[t]); th[t] = 0; }
+    }
+    for (int t = 0; t < nt; t++) {
+        if (nt > 1 && th[t]) pthread_join(th[t], NULL);
+        ok &= job[t].ok;
+    }
+    close(fd);
+    if (!ok) { free(buf); errno = EIO; return NULL; }
+    buf[n] = 0;
+    *len = n;
     return buf;
 }
 
@@ -100,75 +135,92 @@ static inline const char *scan_int(const char *p, long long *out)
 }
 
 /* Parallel path for the shape lda_pre.py writes (one document per line, lda_pre.py:94):
- * the buffer is cut at newlines into one piece per thread, every thread parses its lines
- * into its own arrays, and the pieces are concatenated in order.  A line that does not
- * hold exactly "N" and N "w:c" tokens makes the piece report failure, and the caller falls
- * back to the sequential parser below, which accepts any whitespace like fscanf does. */
+ * the buffer is cut at newlines into one piece per thread.  Pass 1 counts each piece's documents
+ * (non-blank lines) and pairs (':' characters), a prefix sum gives every piece its place in the
+ * final arrays, pass 2 parses straight into them -- no per-thread arrays, no merge copy.  A line
+ * that does not hold exactly "N" and N "w:c" tokens, or a piece whose parse disagrees with its
+ * counts, makes the caller fall back to the sequential parser below, which accepts any whitespace
+ * like fscanf does. */
 typedef struct {
     const char *beg, *end;
-    int64_t *len;      /* pairs per document */
+    size_t ndocs, npairs;        /* pass 1 */
+    int64_t *len;                /* pass 2: pairs per document, at this piece's place */
     int32_t *word, *count;
-    size_t ndocs, npairs, cap_docs, cap_pairs;
     long long nterms;
     int ok;
 } parse_piece;
+
+static void *count_piece(void *arg)
+{
+    parse_piece *pc = arg;
+    size_t docs = 0, pairs = 0;
+    int seen = 0;
+    for (const char *p = pc->beg; p < pc->end; p++) {
+        const char ch = *p;
+        if (ch == '\n') { docs += (size_t)seen; seen = 0; }
+        else if (ch == ':') { pairs++; seen = 1; }
+        else if (ch != ' ' && ch != '\t' && ch != '\r') seen = 1;
+    }
+    pc->ndocs = docs + (size_t)seen;
+    pc->npairs = pairs;
+    return NULL;
+}
 
 static void *parse_lines(void *arg)
 {
     parse_piece *pc = arg;
     const char *p = pc->beg;
-    pc->ok = 1;
+    size_t nd = 0, np = 0;
+    long long nterms = 0;
+    pc->ok = 0;
     while (p < pc->end) {
         while (p < pc->end && (*p == ' ' || *p == '\t' || *p == '\r')) p++;
         if (p >= pc->end) break;
         if (*p == '\n') { p++; continue; }  /* blank line */
         long long n;
         const char *q = scan_int(p, &n);
-        if (!q || n < 0) { pc->ok = 0; return NULL; }
+        if (!q || n < 0) return NULL;
         p = q;
-        if (pc->ndocs == pc->cap_docs) {
-            pc->cap_docs = pc->cap_docs ? pc->cap_docs * 2 : 4096;
-            void *nl = realloc(pc->len, sizeof(int64_t) * pc->cap_docs);
-            if (!nl) { pc->ok = 0; return NULL; }  /* (the old block stays owned by pc and is freed by the caller) */
-            pc->len = nl;
-        }
-        if (pc->npairs + (size_t)n > pc->cap_pairs) {
-            while (pc->npairs + (size_t)n > pc->cap_pairs) pc->cap_pairs = pc->cap_pairs ? pc->cap_pairs * 2 : 65536;
-            void *nw = realloc(pc->word, sizeof(int32_t) * pc->cap_pairs);
-            if (nw) pc->word = nw;
-            void *nc = realloc(pc->count, sizeof(int32_t) * pc->cap_pairs);
-            if (nc) pc->count = nc;
-            if (!nw || !nc) { pc->ok = 0; return NULL; }
-        }
+        if (nd >= pc->ndocs || np + (size_t)n > pc->npairs) return NULL;  /* disagrees with pass 1 */
         for (long long i = 0; i < n; i++) {
             long long w, c;
             while (*p == ' ' || *p == '\t') p++;
             q = scan_int(p, &w);
-            if (!q || *q != ':' || w < 0 || w > 0x7ffffffe) { pc->ok = 0; return NULL; }
+            if (!q || *q != ':' || w < 0 || w > 0x7ffffffe) return NULL;
             q = scan_int(q + 1, &c);
-            if (!q) { pc->ok = 0; return NULL; }
+            if (!q) return NULL;
             p = q;
-            pc->word[pc->npairs] = (int32_t)w;
-            pc->count[pc->npairs] = (int32_t)c;
-            pc->npairs++;
-            if (w >= pc->nterms) pc->nterms = w + 1;
+            pc->word[np] = (int32_t)w;
+            pc->count[np] = (int32_t)c;
+            np++;
+            if (w >= nterms) nterms = w + 1;
         }
         while (*p == ' ' || *p == '\t' || *p == '\r') p++;
         if (*p == '\n') p++;
-        else if (*p != 0) { pc->ok = 0; return NULL; }  /* more tokens on the line: not line-shaped */
-        pc->len[pc->ndocs++] = n;
+        else if (*p != 0) return NULL;  /* more tokens on the line: not line-shaped */
+        pc->len[nd++] = n;
     }
+    pc->nterms = nterms;
+    pc->ok = (nd == pc->ndocs && np == pc->npairs);
     return NULL;
+}
+
+static void run_pieces(parse_piece *pc, int nt, void *(*fn)(void *))
+{
+    pthread_t th[32];
+    for (int t = 0; t < nt; t++)
+        if (nt == 1 || pthread_create(&th[t], NULL, fn, &pc[t]) != 0) { fn(&pc[t]); th[t] = 0; }
+    for (int t = 0; t < nt; t++)
+        if (nt > 1 && th[t]) pthread_join(th[t], NULL);
 }
 
 static int read_corpus_parallel(char *buf, size_t len, oni_lda_corpus *out)
 {
-    enum { MAXT = 8 };
+    enum { MAXT = 32 };
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
     int nt = (int)(ncpu < 1 ? 1 : (ncpu > MAXT ? MAXT : ncpu));
     if (len < ((size_t)1 << 20)) nt = 1;
     parse_piece pc[MAXT];
-    pthread_t th[MAXT];
     memset(pc, 0, sizeof pc);
     const char *cut = buf;
     for (int t = 0; t < nt; t++) {
@@ -179,39 +231,32 @@ static int read_corpus_parallel(char *buf, size_t len, oni_lda_corpus *out)
         if (want < buf + len) want++;  /* the piece ends after its newline */
         pc[t].end = cut = want;
     }
-    for (int t = 0; t < nt; t++)
-        if (nt == 1 || pthread_create(&th[t], NULL, parse_lines, &pc[t]) != 0) { parse_lines(&pc[t]); th[t] = 0; }
-    int ok = 1;
+    run_pieces(pc, nt, count_piece);
     size_t ndocs = 0, npairs = 0;
+    for (int t = 0; t < nt; t++) { ndocs += pc[t].ndocs; npairs += pc[t].npairs; }
+    if (ndocs > 0x7fffffffu) return 1;
+    int64_t *ptr = malloc(sizeof(int64_t) * (ndocs + 1));
+    int32_t *word = malloc(sizeof(int32_t) * (npairs ? npairs : 1));
+    int32_t *count = malloc(sizeof(int32_t) * (npairs ? npairs : 1));
+    if (!ptr || !word || !count) { free(ptr); free(word); free(count); return 1; }
+    size_t d = 0, k = 0;
+    for (int t = 0; t < nt; t++) {
+        pc[t].len = ptr + 1 + d; pc[t].word = word + k; pc[t].count = count + k;
+        d += pc[t].ndocs; k += pc[t].npairs;
+    }
+    run_pieces(pc, nt, parse_lines);
+    int ok = 1;
     long long nterms = 0;
     for (int t = 0; t < nt; t++) {
-        if (nt > 1 && th[t]) pthread_join(th[t], NULL);
         ok &= pc[t].ok;
-        ndocs += pc[t].ndocs; npairs += pc[t].npairs;
         if (pc[t].nterms > nterms) nterms = pc[t].nterms;
     }
-    int rc = 1;  /* 1 = not line-shaped, use the sequential parser */
-    if (ok && ndocs <= 0x7fffffffu) {
-        int64_t *ptr = malloc(sizeof(int64_t) * (ndocs + 1));
-        int32_t *word = malloc(sizeof(int32_t) * (npairs ? npairs : 1));
-        int32_t *count = malloc(sizeof(int32_t) * (npairs ? npairs : 1));
-        if (ptr && word && count) {
-            size_t d = 0, k = 0;
-            ptr[0] = 0;
-            for (int t = 0; t < nt; t++) {
-                memcpy(word + k, pc[t].word, sizeof(int32_t) * pc[t].npairs);
-                memcpy(count + k, pc[t].count, sizeof(int32_t) * pc[t].npairs);
-                for (size_t i = 0; i < pc[t].ndocs; i++) { k += (size_t)pc[t].len[i]; ptr[++d] = (int64_t)k; }
-            }
-            out->num_docs = (int32_t)ndocs; out->num_terms = (int32_t)nterms; out->nnz = (int64_t)npairs;
-            out->doc_ptr = ptr; out->word = word; out->count = count;
-            rc = 0;
-        } else {
-            free(ptr); free(word); free(count);
-        }
-    }
-    for (int t = 0; t < nt; t++) { free(pc[t].len); free(pc[t].word); free(pc[t].count); }
-    return rc;
+    if (!ok) { free(ptr); free(word); free(count); return 1; }  /* not line-shaped: the sequential parser decides */
+    ptr[0] = 0;
+    for (size_t i = 1; i <= ndocs; i++) ptr[i] += ptr[i - 1];  /* lengths -> offsets */
+    out->num_docs = (int32_t)ndocs; out->num_terms = (int32_t)nterms; out->nnz = (int64_t)npairs;
+    out->doc_ptr = ptr; out->word = word; out->count = count;
+    return 0;
 }
 
 int oni_lda_read_corpus(const char *path, oni_lda_corpus *out)
