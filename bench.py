@@ -536,7 +536,14 @@ def _our_arm(args):
     scaling = args.scaling or ("weak" if args.shape == "month" else "strong")
     V = WORKLOAD["vocab"]
 
-    parity = multi_gpu_parity(rank, world, local, dev) if world > 1 else None
+    parity = None
+    if world > 1:
+        # (the fixture files are the same on every rank of the box: if they are missing, every rank
+        #  fails here, before the first collective of the parity run)
+        if os.path.exists(os.path.join(ROOT, "tests", "golden", "c0_k20", "final.gamma")):
+            parity = multi_gpu_parity(rank, world, local, dev)
+        else:
+            parity = {"error": "tests/golden/c0_k20 is not on this box"}
     m = _em_measure(args, shape, scaling, rank, world, local, dev, with_e2e=True)
     weak = None
     if world > 1 and scaling == "strong" and not args.no_weak:
