@@ -237,13 +237,14 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     //             with the main launch's: ~0.35 us per visit
     //   longest   the same kernel alone on its SMs (one warp per scheduler): 0.2 us per visit
     // A document moves up a tier when its chain at the lower tier's pace would last ~0.8 of the
-    // bulk time: from nnz/19000 pairs to the long tier (flow day on one GPU: capped at 1024; an
-    // eighth of it: 360), from nnz/6000 to the top one.  (Measured and dropped for the middle
+    // bulk time: from nnz/15500 pairs to the long tier (flow day on one GPU: capped at 1024; an
+    // eighth of it: 440 -- profiles/tier_sweep.sh: 360 and 576 both end the main launch ~1 ms later,
+    // 256 and 768 ~4 ms later), from nnz/6000 to the top one.  (Measured and dropped for the middle
     // tier: the main build with one block per SM -- a lone warp of it runs at 1.7 us per visit,
     // slower than at full occupancy -- and twelve long-kernel warps per SM, see estep_long.cuh.)
     // ONI_LDA_LONG_DOC / ONI_LDA_EXCL_DOC override the two thresholds (0 = tier off).
     int long_min = c->long_min;
-    if (c->long_min_auto && c->long_kernel) long_min = (int)std::min<int64_t>(1024, std::max<int64_t>(128, nnz / 19000));
+    if (c->long_min_auto && c->long_kernel) long_min = (int)std::min<int64_t>(1024, std::max<int64_t>(128, nnz / 15500));
     int32_t n_long = 0;
     int64_t pairs_long = 0, max_pairs = 0;
     for (int32_t d = 0; d < D; d++) {
