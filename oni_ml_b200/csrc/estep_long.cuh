@@ -17,13 +17,16 @@
 //                            for five shuffle+add levels
 //   1/S                      MUFU seed + 3
 //
-// ~15 dependent fp64 operations (8.4 cycles each on B200, profiles/micro/lat.cu) + two
-// shared-memory round trips per visit.  A lone warp issues in order and pays ~20 cycles for
-// every branch, so the visit body is straight-line code: what is not on the chain (the bound's
-// sums, phi stores, requests for later rows) is written to be ready when it issues -- ring
-// reads one visit ahead, addresses advanced by increments, dead topic slots handled by zero-fill
-// copies and a zero count instead of tests.  Rows and pairs arrive through a shared-memory ring
-// filled by cp.async QD visits ahead.  Topic k lives in lane k mod 32 (T = ceil(K/32) per lane).
+// ~15 dependent fp64 operations (8.4 cycles each on B200, profiles/micro/lat.cu), a table index
+// five integer operations deep and two shared-memory round trips per visit: ~360-390 cycles measured
+// (0.19-0.20 us; the one-warp build of estep_kernel: 820).  A lone warp issues in order and pays
+// ~20 cycles for every branch, so the visit body is straight-line code and its SOURCE ORDER is the
+// schedule: the new gamma's table reads first, then -- in their shadow -- the previous visit's phi
+// store and bound sums, the requests for later rows and the next visit's ring reads; dead topic
+// slots are handled by zero-fill copies and a zero count instead of tests.  Rows and pairs arrive
+// through a shared-memory ring filled by cp.async QD visits ahead.  Topic k lives in lane k mod 32
+// (T = ceil(K/32) per lane).  History, per-instruction stall samples and what was tried and
+// dropped (twelve warps per SM, a helper warp per document, a tensor-core sum): profiles/r2_longdoc.txt.
 //
 // The psi table covers gamma in [2^-8, 2^23).  A document that leaves it (alpha below 2^-8, or
 // more than 8M tokens on one topic) is run again from its start by the SLOW instantiation
@@ -46,8 +49,10 @@ __device__ __forceinline__ double count_to_double(int n)
 // m8n8k4 product adds the four values of each quad (row g of A = the lanes of quad g), one
 // exchange brings quad sums k and k+4 to lane position k of every quad, and a second product adds
 // those four.  2 DMMA (26 cycles each on B200) + one shuffle + one addition: ~85 cycles and 8
-// instructions, against ~105 cycles and 32 instructions for the exchange through shared memory
-// with a 20-value tree, or ~160 cycles for five shuffle+add levels.
+// instructions on paper, against ~105 cycles and 32 instructions for the exchange through shared
+// memory with a 20-value tree.  MEASURED (build -DONI_LONG_SUM_DMMA): 0.206-0.208 us per visit
+// against 0.204 for the shared-memory tree beside a 125k-document shard -- no gain, so the tree
+// is the default and this stays as the record of the experiment.
 __device__ __forceinline__ double warp_sum_dmma(double v, int lane)
 {
     const double one = 1.0, zero = 0.0;
@@ -126,7 +131,7 @@ __device__ __forceinline__ bool long_document(const EstepParams &p, const LongSh
                                               double inv_k, double lik_const)
 {
     constexpr int QD = LongLayout<T, 4>::QD, QT = LongLayout<T, 4>::QT;
-    #ifndef ONI_LONG_SUM_DMMA
+#ifndef ONI_LONG_SUM_DMMA
     constexpr bool MASK = !(T == 1 && NSUM < 32);  // dead slots could reach the sum
 #else
     constexpr bool MASK = true;                    // every lane's value enters the tensor-core sum
