@@ -81,7 +81,7 @@ def test_single_e_step_matches_oracle(c0_corpus, k, alpha, vmax):
     assert stats["word_visits"] == ref["word_visits"]
 
 
-@pytest.mark.parametrize("k,alpha", [(20, 2.5), (50, 0.3), (100, 0.2), (20, 0.004)])
+@pytest.mark.parametrize("k,alpha", [(20, 2.5), (50, 0.3), (100, 0.2), (20, 0.004), (80, 0.4), (12, 0.9), (32, 1.1)])
 def test_long_document_paths_match_oracle(monkeypatch, k, alpha):
     """The one-document-per-warp build (rows through the cp.async ring, requested 8/4/2 visits ahead
     for 1/2/4 topics per lane) and its exclusive-SM launch, forced onto documents of 64..700 pairs
