@@ -103,6 +103,7 @@ struct oni_lda_ctx {
     bool long_min_auto = false;  // ... chosen per corpus from its size (no ONI_LDA_LONG_DOC)
     int32_t n_long = 0;    // they are the first n_long entries of `order`
     int32_t n_excl = 0;    // the first n_excl of those get an SM to themselves (4 documents per SM)
+    int32_t n_small = 0;   // documents of at most one pair: the LAST n_small entries of `order`
     oni_lda_settings st{};
     int var_max_iter = 0;  // doubles when the bound decreases (lda-estimate.c:261)
     cudaStream_t stream = nullptr, stream_long = nullptr, stream_excl = nullptr;
@@ -199,7 +200,7 @@ void free_corpus(oni_lda_ctx *c)
     cudaFree(c->d_items); cudaFree(c->d_items2); cudaFree(c->d_partial);
     c->d_items = c->d_items2 = nullptr; c->d_partial = nullptr;
     c->cap_items = c->cap_items2 = c->cap_partial = 0;
-    c->D = 0; c->nnz = 0; c->n_long = 0; c->n_excl = 0;
+    c->D = 0; c->nnz = 0; c->n_long = 0; c->n_excl = 0; c->n_small = 0;
 }
 
 double now_seconds();
@@ -247,9 +248,11 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     if (c->long_min_auto && c->long_kernel) long_min = (int)std::min<int64_t>(1024, std::max<int64_t>(128, nnz / 15500));
     int32_t n_long = 0;
     int64_t pairs_long = 0, max_pairs = 0;
+    int32_t n_small = 0;
     for (int32_t d = 0; d < D; d++) {
         const int64_t n = h_ptr[d + 1] - h_ptr[d];
         max_pairs = std::max(max_pairs, n);
+        n_small += n <= 1;
         if (long_min > 0 && n >= long_min) { n_long++; pairs_long += n; }
     }
     int32_t n_excl = 0;
@@ -266,6 +269,7 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     tm.lap("validate doc_ptr");
 
     c->D = D; c->nnz = nnz; c->n_long = n_long; c->n_excl = n_excl; c->max_doc_pairs = max_pairs;
+    c->n_small = std::min<int32_t>(n_small, D - n_long);
     cudaStream_t s = c->stream;
     if (!c->d_doc_ptr || (size_t)D > c->cap_docs || (size_t)nnz > c->cap_pairs) {
         // (one of the two grew: everything sized by it is replaced; sizes are kept with a little headroom)
@@ -529,7 +533,7 @@ static int create_impl(int32_t device, int32_t K, int32_t V, const oni_lda_setti
     ONI_TRY(dev_alloc(&c->d_alpha, 1));
     ONI_TRY(dev_alloc(&c->d_ss, c->ss_count()));
     ONI_TRY(dev_alloc(&c->d_block_partial, (size_t)DOC_RED_BLOCKS * 3));
-    ONI_TRY(dev_alloc(&c->d_ticket, 3));
+    ONI_TRY(dev_alloc(&c->d_ticket, 4));
     ONI_TRY(dev_alloc(&c->d_done, 1));
     ONI_TRY(dev_alloc(&c->d_nan, 1));
     ONI_CUDA(cudaMemset(c->d_done, 0, sizeof(unsigned)));
@@ -722,7 +726,7 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
     const bool use_long = c->long_kernel && !shift && c->model_min > -1.0e5 &&
                           (double)c->max_doc_pairs * c->KP < 4.0e9;
 
-    ONI_CUDA(cudaMemsetAsync(c->d_ticket, 0, 3 * sizeof(unsigned), s));
+    ONI_CUDA(cudaMemsetAsync(c->d_ticket, 0, 4 * sizeof(unsigned), s));
     ONI_CUDA(cudaEventRecord(c->ev[0], s));
     if (c->n_long > 0) ONI_CUDA(cudaEventRecord(c->ev_fork, s));
     if (c->n_excl > 0) {
@@ -758,13 +762,26 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         ONI_CUDA(cudaEventRecord(c->ev_join, c->stream_long));
         ONI_CUDA(cudaEventRecord(c->ev_t_long, c->stream_long));
     }
-    if (c->D > c->n_long) {
+    if (c->D - c->n_small > c->n_long) {
         EstepParams ps = p;
         ps.order = c->d_order + c->n_long;
-        ps.D = c->D - c->n_long;
+        ps.D = c->D - c->n_long - c->n_small;
         cudaError_t e = launch_estep(c->G, c->T, shift, ps, c->sm_count, s);
         if (e != cudaSuccess)
             return oni_set_error(ONI_ERR_CUDA, "E-step launch (G=%d,T=%d): %s", c->G, c->T, cudaGetErrorString(e));
+        c->launches++;
+    }
+    if (c->n_small > 0) {
+        // documents of one pair (and empty ones) last, through the build that knows a document's only
+        // row is both the one it writes and the next one it reads
+        EstepParams pt = p;
+        pt.order = c->d_order + (c->D - c->n_small);
+        pt.D = c->n_small;
+        pt.ticket = c->d_ticket + 3;
+        pt.no_exact = 1;
+        cudaError_t e = launch_estep(c->G, c->T, shift, pt, c->sm_count, s);
+        if (e != cudaSuccess)
+            return oni_set_error(ONI_ERR_CUDA, "E-step launch (one-pair documents): %s", cudaGetErrorString(e));
         c->launches++;
     }
     ONI_CUDA(cudaEventRecord(c->ev_t_main, s));

@@ -113,6 +113,7 @@ struct EstepParams {
     int32_t D, K, KP;
     int32_t var_max_iter;      // -1 = no cap
     double var_converged;
+    int32_t no_exact;          // 1: not the exact-fit build (this launch may hold one-pair documents)
     const double *psi_tab;     // long-document kernel only (psi_table.h): [PSI_N][6]
     const double *exk_tab;     // ... [EXK_N]
 };
@@ -267,7 +268,8 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
     double acc_s = 0.0;               // SHIFT only: sum c*shift (same in every lane)
     double s_keep = 1.0, c_keep = 0.0;
     double lik_old = 0.0;
-    int64_t beg = 0, end = 0, pos = 0;
+    // pair positions fit 32 bits (a shard holds fewer than 2^31 pairs, checked when it is indexed)
+    uint32_t beg = 0, end = 0, pos = 0;
     int32_t doc = -1, pass = 0;
     int2 tk = make_int2(0, 0);   // (word, count) of the pair at `pos`
     int2 tk1 = make_int2(0, 0);  // ... and of the visit after it
@@ -283,8 +285,8 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
                 exhausted = true;
             } else {
                 doc = p.order[i];
-                beg = p.doc_ptr[doc];
-                end = p.doc_ptr[doc + 1];
+                beg = (uint32_t)p.doc_ptr[doc];
+                end = (uint32_t)p.doc_ptr[doc + 1];
                 pos = beg;
                 pass = 0;
                 lik_old = 0.0;
@@ -354,9 +356,9 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
                     lbc[t] = my_lb[(sr * T + t) * 32];
                     oldc[t] = my_old[(sr * T + t) * 32];  // (not used during the first sweep)
                 }
-                const int64_t len = end - beg;
-                const int64_t rpos = (pos + QD < end) ? pos + QD : pos + QD - len;
-                const int64_t tpos = (pos + QT < end) ? pos + QT : pos + QT - len;
+                const uint32_t len = end - beg;
+                const uint32_t rpos = (pos + QD < end) ? pos + QD : pos + QD - len;
+                const uint32_t tpos = (pos + QT < end) ? pos + QT : pos + QT - len;
                 const int2 rtk = my_tk[((vi + QD) & (QT - 1)) * 32];
                 const double *nlb = p.logbeta_t + (size_t)rtk.x * KP;
                 const double *nph = p.phi + (size_t)rpos * KP;
@@ -376,14 +378,14 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             // Software pipeline: the rows of the NEXT visit (wrapping to the first word
             // for the next sweep) are requested now and consumed one visit later, so
             // their latency hides behind this visit's arithmetic.
-            const int64_t npos = (pos + 1 < end) ? pos + 1 : beg;
-            const int64_t n2pos = (npos + 1 < end) ? npos + 1 : beg;
+            const uint32_t npos = (pos + 1 < end) ? pos + 1 : beg;
+            const uint32_t n2pos = (npos + 1 < end) ? npos + 1 : beg;
             int2 tk2 = make_int2(0, 0);
             if (!RING) tk2 = __ldg(p.tok + n2pos);
             if (ONI_ESTEP_PF_AHEAD > 0 && pass > 0 && j * 128 < KP * 8 + 127) {
                 // the phi rows stream from HBM (every sweep rereads what the last one wrote);
                 // pull the row of a later visit into L2 so the register load above finds it there
-                const int64_t fpos = pos + ONI_ESTEP_PF_AHEAD;
+                const uint32_t fpos = pos + ONI_ESTEP_PF_AHEAD;
                 if (fpos < end) prefetch_l2(reinterpret_cast<const char *>(p.phi + (size_t)fpos * KP) + j * 128);
             }
             const bool next_first_sweep = (pass == 0) && (npos != beg);
@@ -500,7 +502,9 @@ __global__ void ONI_ESTEP_BOUNDS estep_kernel(const EstepParams p)
             // one-word document: the row just written is the next "old".  (Compiled out of the
             // long-document kernel: it becomes a select on the in-flight load and cost a lone
             // long document a quarter of its time.)
-            if (!LONGDOC && npos == pos) {
+            // (the exact-fit build is never given one-pair documents: the engine launches those
+            //  separately, which takes ten selects out of every visit of everything else)
+            if (!LONGDOC && !EXACT && npos == pos) {
 #pragma unroll
                 for (int t = 0; t < T; t++) oldc[t] = x[t];
             }
