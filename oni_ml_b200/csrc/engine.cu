@@ -37,6 +37,7 @@
 
 using namespace oni;
 
+static const int TIER_LEN_CAP = 65535;  // document lengths above it share one bucket of docs_ge
 static const MathTables g_host_tables = ONI_MATH_TABLES_INIT;  // host copy (digamma_ref on the host)
 
 // ----------------------------------------------------------------- NCCL, lazily
@@ -103,6 +104,7 @@ struct oni_lda_ctx {
     bool long_min_auto = false;  // ... chosen per corpus from its size (no ONI_LDA_LONG_DOC)
     int32_t n_long = 0;    // they are the first n_long entries of `order`
     int32_t n_excl = 0;    // the first n_excl of those get an SM to themselves (4 documents per SM)
+    std::vector<int32_t> docs_ge;  // docs_ge[L] = documents of >= L pairs (L <= TIER_LEN_CAP); empty = tiers fixed
     int32_t n_small = 0;   // documents of at most one pair: the LAST n_small entries of `order`
     oni_lda_settings st{};
     int var_max_iter = 0;  // doubles when the bound decreases (lda-estimate.c:261)
@@ -249,12 +251,19 @@ int build_indices(oni_lda_ctx *c, int32_t D, int64_t nnz, const int64_t *h_ptr, 
     int32_t n_long = 0;
     int64_t pairs_long = 0, max_pairs = 0;
     int32_t n_small = 0;
+    const bool retier = c->long_min_auto && c->long_kernel && !getenv("ONI_LDA_EXCL_DOC") && c->G_long == 32 &&
+                        c->T_long <= 4 && !(getenv("ONI_LDA_RETIER") && atoi(getenv("ONI_LDA_RETIER")) == 0);
+    c->docs_ge.clear();
+    if (retier) c->docs_ge.assign(TIER_LEN_CAP + 2, 0);
     for (int32_t d = 0; d < D; d++) {
         const int64_t n = h_ptr[d + 1] - h_ptr[d];
         max_pairs = std::max(max_pairs, n);
         n_small += n <= 1;
         if (long_min > 0 && n >= long_min) { n_long++; pairs_long += n; }
+        if (retier) c->docs_ge[std::min<int64_t>(n, TIER_LEN_CAP)]++;
     }
+    if (retier)
+        for (int L = TIER_LEN_CAP - 1; L >= 0; L--) c->docs_ge[L] += c->docs_ge[L + 1];
     int32_t n_excl = 0;
     int64_t pairs_excl = 0;
     if (n_long > 0 && c->G_long == 32 && c->T_long <= 4) {
@@ -866,6 +875,29 @@ static int launch_m_step(oni_lda_ctx *c)
     return ONI_OK;
 }
 
+// After an EM iteration the number of word visits is known, and with it how long the bulk of the
+// next E-step will take (~0.107 ns per visit at K = 20 with the GPU full); the tier thresholds of
+// build_indices, which had to guess it from the pair count, are set again from it: a document's
+// chain in the main launch (~1.26 us per visit of one document, var_max_iter sweeps at worst) and
+// in the co-resident long launch (~0.39 us) should both end at ~0.9 of the bulk.  A corpus whose
+// documents converge in few sweeps (DNS day) gets its long tier from ~570 pairs instead of 1024 on
+// four GPUs.  The visit count is a sum over all ranks' documents and does not depend on timing, so a
+// run stays reproducible; the tiers are prefixes of the same length-sorted order.
+static void retier_from_visits(oni_lda_ctx *c)
+{
+    if (c->docs_ge.empty() || c->stats.word_visits <= 0) return;
+    const double visits = (double)c->stats.word_visits / std::max(1, c->nranks);
+    const double sweeps = c->var_max_iter > 0 ? std::min(c->var_max_iter, 1000) : 20;
+    const double bulk_us = visits * 0.107e-3 * (c->K / 20.0);
+    const int64_t long_min = std::min<int64_t>(1024, std::max<int64_t>(128, (int64_t)(0.9 * bulk_us / (sweeps * 1.26))));
+    const int64_t excl_min = std::min<int64_t>(TIER_LEN_CAP, std::max<int64_t>(long_min, (int64_t)(0.9 * bulk_us / (sweeps * 0.39))));
+    const int32_t n_long = c->docs_ge[long_min];
+    const int32_t n_excl = std::min(std::min(c->docs_ge[excl_min], n_long), 4 * std::max(1, c->sm_count / 8));
+    c->n_long = n_long;
+    c->n_excl = n_excl;
+    c->n_small = std::min<int32_t>(c->n_small, c->D - n_long);
+}
+
 static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
 {
     ONI_CUDA(cudaStreamSynchronize(c->stream));
@@ -906,6 +938,7 @@ static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
     // from then on) and without an overflow guard; here "no cap" stays "no cap" and the doubling
     // stops at 2^30
     if (c->converged < 0 && c->var_max_iter > 0 && c->var_max_iter < (1 << 30)) c->var_max_iter *= 2;
+    retier_from_visits(c);
     c->lik_old = lik;
     c->estep_done = false;
     if (likelihood) *likelihood = lik;
