@@ -207,7 +207,7 @@ typedef struct {
     double ms_estep_kernel;  /* CUDA-event time of the per-document kernel    */
     double ms_suffstats;     /* deterministic reduction kernels               */
     double ms_mstep;         /* M-step + alpha kernels                        */
-    int64_t word_visits;     /* sum over docs of pairs x passes               */
+    int64_t word_visits;     /* sum over this rank's docs of pairs x passes   */
     int64_t kernel_launches; /* kernels launched by the library so far        */
     /* where the E-step's time goes: its three launches overlap on three streams; each   */
     /* figure is the time from the start of the E-step to the END of that launch (ms;   */

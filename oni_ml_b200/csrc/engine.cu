@@ -809,6 +809,8 @@ extern "C" int oni_lda_e_step(oni_lda_ctx *c)
         c->launches += 2;
     }
     ONI_CUDA(cudaEventRecord(c->ev[2], s));
+    // this rank's own visit count, before an all-reduce sums the tail over the ranks
+    ONI_CUDA(cudaMemcpyAsync(c->h_pinned + 6, c->ss_tail() + 3, sizeof(double), cudaMemcpyDeviceToHost, s));
     ONI_CUDA(cudaGetLastError());
     c->estep_done = true;
     return ONI_OK;
@@ -881,12 +883,12 @@ static int launch_m_step(oni_lda_ctx *c)
 // chain in the main launch (~1.26 us per visit of one document, var_max_iter sweeps at worst) and
 // in the co-resident long launch (~0.39 us) should both end at ~0.9 of the bulk.  A corpus whose
 // documents converge in few sweeps (DNS day) gets its long tier from ~570 pairs instead of 1024 on
-// four GPUs.  The visit count is a sum over all ranks' documents and does not depend on timing, so a
+// four GPUs.  The visit count is a property of the documents and the model, not of timing, so a
 // run stays reproducible; the tiers are prefixes of the same length-sorted order.
 static void retier_from_visits(oni_lda_ctx *c)
 {
     if (c->docs_ge.empty() || c->stats.word_visits <= 0) return;
-    const double visits = (double)c->stats.word_visits / std::max(1, c->nranks);
+    const double visits = (double)c->stats.word_visits;  // (this rank's shard)
     const double sweeps = c->var_max_iter > 0 ? std::min(c->var_max_iter, 1000) : 20;
     const double bulk_us = visits * 0.107e-3 * (c->K / 20.0);
     const int64_t long_min = std::min<int64_t>(1024, std::max<int64_t>(128, (int64_t)(0.9 * bulk_us / (sweeps * 1.26))));
@@ -906,7 +908,7 @@ static int finish_m_step(oni_lda_ctx *c, double *likelihood, double *converged)
     const double lik = c->h_pinned[1];
     c->alpha = c->h_pinned[4];
     c->model_min = c->model_min_rowmax = -100.0;  // the table is lda_mle's now (floor: lda-model.c:42)
-    c->stats.word_visits = (int64_t)c->h_pinned[3];
+    c->stats.word_visits = (int64_t)c->h_pinned[6];
     float ms = 0;
     if (cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) c->stats.ms_estep_kernel = ms;
     {
