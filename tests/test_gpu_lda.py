@@ -144,6 +144,37 @@ def test_long_document_leaves_the_digamma_table(monkeypatch):
     assert int((np.diff(ptr) * it1).sum()) == ref["word_visits"]
 
 
+def test_tier_thresholds_follow_the_visit_count(monkeypatch):
+    """After the first EM iteration the engine re-derives which documents run on the long-document
+    launches from the shard's visit count (retier_from_visits, csrc/engine.cu).  That is scheduling
+    only: the run with it and the run with the pair-count rule alone (ONI_LDA_RETIER=0) must give the
+    same bound, alpha and gamma, although some documents change kernels between iterations."""
+    monkeypatch.delenv("ONI_LDA_LONG_DOC", raising=False)
+    monkeypatch.delenv("ONI_LDA_EXCL_DOC", raising=False)
+    V, k = 20000, 20
+    c = synth_corpus(200_000, V, mu=3.5, seed=77)
+    st = _lib.Settings(20, 1e-6, 20, 1e-6, 1)
+    runs = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("ONI_LDA_RETIER", mode)
+        with lda.LdaEngine(0, k, V, st) as eng:
+            eng.set_corpus(c)
+            eng.init_random(3, 2.5)
+            liks, tiers = [], []
+            for _ in range(3):
+                liks.append(eng.em_iteration()[0])
+                s = eng.stats()
+                tiers.append((s["docs_exclusive"], s["docs_long"]))
+            runs[mode] = (liks, tiers, eng.gamma(), eng.alpha(), s["word_visits"])
+    (l0, t0, g0, a0, v0), (l1, t1, g1, a1, v1) = runs["0"], runs["1"]
+    assert t0[0] == t0[1] == t0[2] and sum(t0[0]) > 0  # the pair-count rule does not move
+    assert t1[0] == t0[0]                               # first iteration: nothing known yet
+    assert t1[1] != t0[1]                               # then the visit count decides
+    assert v0 == v1
+    assert rel_err(l1, l0) < 1e-11 and abs(a1 - a0) / a0 < 1e-10
+    assert rel_err(g1, g0) < 1e-8
+
+
 def test_loaded_model_with_an_underflowing_word(c0_corpus):
     """A model that did not come from this engine's M-step (set_model / `lda inf` / a model-root
     start) may hold a word whose every topic sits far below the -100 floor.  exp(digamma + log
